@@ -1,0 +1,537 @@
+// libdba C ABI (include/dba.h): context, plan cache, workspace, the LM iteration loop and the
+// optional NCCL all-reduce of the reduced system for sharded global BA.
+#include "../../include/dba.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "dba_kernels.h"
+#include "dba_plan.h"
+
+namespace dba {
+thread_local int64_t g_launch_count = 0;
+}
+
+using namespace dba;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes, bool zero = false) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) return e;
+    cap = want;
+    if (zero) e = cudaMemset(p, 0, want);
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// ---- NCCL through dlopen: the single-GPU path has no NCCL dependency ---------------------------
+struct Id128 { char b[128]; };
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, /*ncclUniqueId by value*/ Id128, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+bool load_nccl(std::string& err) {
+  if (g_nccl.lib) return true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.lib) break;
+  }
+  if (!g_nccl.lib) { err = "libnccl.so.2 not found (import torch first, or add it to LD_LIBRARY_PATH)"; return false; }
+  g_nccl.GetUniqueId = reinterpret_cast<decltype(g_nccl.GetUniqueId)>(dlsym(g_nccl.lib, "ncclGetUniqueId"));
+  g_nccl.CommInitRank = reinterpret_cast<decltype(g_nccl.CommInitRank)>(dlsym(g_nccl.lib, "ncclCommInitRank"));
+  g_nccl.AllReduce = reinterpret_cast<decltype(g_nccl.AllReduce)>(dlsym(g_nccl.lib, "ncclAllReduce"));
+  g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(dlsym(g_nccl.lib, "ncclCommDestroy"));
+  g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(dlsym(g_nccl.lib, "ncclGetErrorString"));
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) {
+    err = "NCCL symbols missing";
+    return false;
+  }
+  return true;
+}
+
+}  // namespace
+
+struct dba_ctx {
+  int device = 0;
+  std::string err;
+  // options
+  bool block_diag_quirk = false;
+  bool keep_system = false;
+  int opt_splits = 0;
+  int opt_ppl = 0;
+  // plan cache
+  Plan plan;
+  bool plan_valid = false;
+  int plan_ppl = 0, plan_tps = 1, plan_HW = 0;
+  DevBuf d_plan_i32, d_items;
+  DeviceGraph g{};
+  // workspace
+  DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Ldiag, dx, dz, fail, Akeep;
+  // host staging
+  int64_t* h_idx = nullptr;
+  size_t h_idx_cap = 0;
+  // host-entry staging (dba_ba_host)
+  DevBuf s_poses, s_disps, s_intr, s_sens, s_targets, s_weights, s_eta, s_ii, s_jj, s_dx, s_dz;
+  // NCCL
+  void* comm = nullptr;
+  int nranks = 1, rank = 0;
+  int64_t last_launches = 0;
+  size_t smem_cap = 0;
+};
+
+namespace {
+
+int fail_arg(dba_ctx* c, const std::string& m) { c->err = m; return -1; }
+int fail_cuda(dba_ctx* c, cudaError_t e, const char* where) {
+  c->err = std::string(where) + ": " + cudaGetErrorString(e);
+  return int(e) > 0 ? int(e) : 999;
+}
+#define CK(call, where)                                      \
+  do {                                                       \
+    cudaError_t e__ = (call);                                \
+    if (e__ != cudaSuccess) return fail_cuda(ctx, e__, where); \
+  } while (0)
+
+int out_degree_max(const int64_t* ii, int64_t E, int N, int* M_out) {
+  std::vector<int> deg(N, 0);
+  int mx = 0, M = 0;
+  for (int64_t e = 0; e < E; ++e)
+    if (ii[e] >= 0 && ii[e] < N) { if (deg[ii[e]]++ == 0) ++M; if (deg[ii[e]] > mx) mx = deg[ii[e]]; }
+  *M_out = M;
+  return mx;
+}
+
+// (re)build the plan for this graph if it differs from the cached one, upload it
+int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, int N, int ht, int wd, int64_t M,
+                 int t0, int t1, bool motion_only, cudaStream_t st) {
+  const int HW = ht * wd;
+  Plan& P = ctx->plan;
+  bool same = ctx->plan_valid && P.E == E && P.N == N && P.t0 == t0 && P.t1 == t1 && P.motion_only == motion_only &&
+              ctx->plan_HW == HW && int64_t(P.key_ii.size()) == E &&
+              (E == 0 || (std::memcmp(P.key_ii.data(), ii, E * sizeof(int64_t)) == 0 &&
+                          std::memcmp(P.key_jj.data(), jj, E * sizeof(int64_t)) == 0));
+  if (same) {
+    if (!motion_only && M >= 0 && M != P.M) return fail_arg(ctx, "eta rows != |unique(ii)|");
+    return 0;
+  }
+  ctx->plan_valid = false;
+  if (E > 0) {
+    for (int64_t e = 0; e < E; ++e)
+      if (ii[e] < 0 || ii[e] >= N) return fail_arg(ctx, "edge index outside the frame buffer");
+  }
+  int Mq = 0;
+  const int degmax = out_degree_max(ii, E, N, &Mq);
+  int ppl = ctx->opt_ppl > 0 ? ctx->opt_ppl : linearize_pick_ppl(degmax, degmax + 1, motion_only, HW, ctx->smem_cap);
+  if (ppl == 0 || linearize_smem_bytes(degmax, ppl, motion_only) > ctx->smem_cap)
+    return fail_arg(ctx, "a source keyframe has too many outgoing edges for the shared-memory panel (limit ~200)");
+  const int T = 32 * ppl;
+  const int ntilesT = (HW + T - 1) / T;
+  int S = ctx->opt_splits;
+  if (S <= 0) {
+    int sm = 148;
+    cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, ctx->device);
+    S = (4 * sm + (Mq > 0 ? Mq : 1) - 1) / (Mq > 0 ? Mq : 1);
+  }
+  if (S > ntilesT) S = ntilesT;
+  if (S < 1) S = 1;
+  const int tps = (ntilesT + S - 1) / S;
+  S = (ntilesT + tps - 1) / tps;     // no empty split
+  if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
+  ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW;
+
+  // non-source frames of [0,t1)
+  std::vector<int32_t> nonsrc;
+  for (int f = 0; f < t1; ++f) if (P.slot_of_frame[f] < 0) nonsrc.push_back(f);
+
+  // pack all int32 arrays into one upload
+  std::vector<int32_t> pack;
+  auto put = [&](const std::vector<int32_t>& v) {
+    size_t off = pack.size();
+    pack.insert(pack.end(), v.begin(), v.end());
+    while (pack.size() % 4) pack.push_back(0);
+    return off;
+  };
+  size_t o_kx = put(P.kx), o_koff = put(P.koff), o_cedge = put(P.cedge), o_ci = put(P.ci), o_cj = put(P.cj);
+  size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
+  CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
+  CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
+  std::vector<Item> items(P.sblk_items);
+  const size_t n_s = items.size();
+  items.insert(items.end(), P.rhs_items.begin(), P.rhs_items.end());
+  CK(ctx->d_items.ensure(items.size() * sizeof(Item) + 16), "plan alloc");
+  if (!items.empty())
+    CK(cudaMemcpyAsync(ctx->d_items.p, items.data(), items.size() * sizeof(Item), cudaMemcpyHostToDevice, st),
+       "plan upload");
+  CK(cudaStreamSynchronize(st), "plan upload");   // host vectors go out of scope
+
+  DeviceGraph& g = ctx->g;
+  const int32_t* base = ctx->d_plan_i32.as<int32_t>();
+  g.E = P.E; g.N = N; g.t0 = t0; g.t1 = t1; g.Pp = P.Pp; g.M = P.M; g.n6 = P.n6; g.S = P.S;
+  g.degmax = P.degmax; g.nblkmax = P.nblkmax; g.npairs_max = P.npairs_max;
+  g.HW = HW; g.ht = ht; g.wd = wd;
+  g.kx = base + o_kx; g.koff = base + o_koff; g.cedge = base + o_cedge; g.ci = base + o_ci; g.cj = base + o_cj;
+  g.pairbase = base + o_pb; g.blkbase = base + o_bb; g.nonsrc = base + o_ns; g.n_nonsrc = int(nonsrc.size());
+  g.sblk_off = base + o_so; g.rhs_off = base + o_ro;
+  g.sblk_items = ctx->d_items.as<Item>();
+  g.rhs_items = ctx->d_items.as<Item>() + n_s;
+  g.nSblk = P.nSblk;
+  ctx->plan_valid = true;
+  return 0;
+}
+
+int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
+  const Plan& P = ctx->plan;
+  const size_t HW = size_t(ctx->plan_HW);
+  const size_t f = sizeof(float);
+  CK(ctx->Hpart.ensure(size_t(P.E) * P.S * 32 * f + 16), "workspace");
+  CK(ctx->Spart.ensure(size_t(P.slab_blocks) * 36 * f + 16), "workspace");
+  CK(ctx->vEpart.ensure(size_t(P.vE_blocks) * 6 * f + 16), "workspace");
+  CK(ctx->Q.ensure(size_t(P.M) * HW * f + 16), "workspace");
+  CK(ctx->w.ensure(size_t(P.M) * HW * f + 16), "workspace");
+  CK(ctx->dz.ensure(size_t(P.M) * HW * f + 16), "workspace");
+  CK(ctx->Hblk.ensure(size_t(P.E) * 144 * f + 16), "workspace");
+  CK(ctx->vblk.ensure(size_t(P.E) * 12 * f + 16), "workspace");
+  const int ld = (P.n6 + 1 + 3) & ~3;
+  CK(ctx->A.ensure(size_t(P.n6 + 1) * ld * f, true), "workspace");
+  const int nkb = (P.n6 + 31) / 32;
+  CK(ctx->Ldiag.ensure(size_t(nkb) * 1024 * f), "workspace");
+  CK(ctx->dx.ensure(size_t(P.n6) * f + 16), "workspace");
+  CK(ctx->fail.ensure(16, true), "workspace");
+  if (ctx->keep_system) CK(ctx->Akeep.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
+  ws.Hpart = ctx->Hpart.as<float>(); ws.Spart = ctx->Spart.as<float>(); ws.vEpart = ctx->vEpart.as<float>();
+  ws.Q = ctx->Q.as<float>(); ws.w = ctx->w.as<float>(); ws.Hblk = ctx->Hblk.as<float>(); ws.vblk = ctx->vblk.as<float>();
+  ws.A = ctx->A.as<float>(); ws.ldA = ld; ws.Ldiag = ctx->Ldiag.as<float>(); ws.dx = ctx->dx.as<float>();
+  ws.dz = ctx->dz.as<float>(); ws.fail = ctx->fail.as<int>();
+  return 0;
+}
+
+// The iteration loop on device pointers; ii/jj here are HOST copies of the edge lists.
+int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const float* disps_sens,
+           const float* targets, const float* weights, const float* eta, const int64_t* ii_h, const int64_t* jj_h,
+           int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+           bool motion_only, float* dx_out, float* dz_out, cudaStream_t st) {
+  g_launch_count = 0;
+  int rc = prepare_plan(ctx, ii_h, jj_h, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only, st);
+  if (rc) return rc;
+  Workspace ws{};
+  rc = ensure_workspace(ctx, ws);
+  if (rc) return rc;
+  const DeviceGraph& g = ctx->g;
+  BAInputs in{poses, disps, intr, disps_sens, targets, weights, eta};
+  // sharded: every rank damps its share of H; the constant ep is added once (rank 0)
+  const float ep_eff = (ctx->rank == 0) ? ep : 0.f;
+  for (int it = 0; it < iterations; ++it) {
+    if (g.E > 0) CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, st), "linearize");
+    CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
+    if (ctx->comm != nullptr && ctx->nranks > 1) {
+      const size_t cnt = size_t(g.n6 + 1) * ws.ldA;
+      int r = g_nccl.AllReduce(ws.A, ws.A, cnt, /*ncclFloat32*/ 7, /*ncclSum*/ 0, ctx->comm, st);
+      if (r != 0) {
+        ctx->err = std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+        return 1000 + r;
+      }
+    }
+    if (ctx->keep_system)
+      CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
+         "keep_system");
+    CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
+    if (!motion_only && g.E > 0) CK(launch_backsub(g, in, ws, st), "backsub");
+    CK(launch_retract(g, in, ws, (it == iterations - 1) ? dx_out : nullptr, st), "retract");
+  }
+  if (!motion_only && iterations > 0) {
+    CK(launch_guard_nonsrc(g, in, st), "guard");
+    if (dz_out != nullptr && g.M > 0)
+      CK(cudaMemcpyAsync(dz_out, ws.dz, size_t(g.M) * g.HW * sizeof(float), cudaMemcpyDeviceToDevice, st), "dz_out");
+  }
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int check_common(dba_ctx* ctx, const void* poses, const void* disps, const void* intr, const void* targets,
+                 const void* weights, const void* eta, const void* ii, const void* jj, int64_t E, int64_t N, int ht,
+                 int wd, int64_t M, int iterations, int motion_only) {
+  if (!ctx) return -1;
+  if (!poses || !disps || !intr) return fail_arg(ctx, "poses / disps / intrinsics must not be NULL");
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || iterations < 0) return fail_arg(ctx, "negative or zero size");
+  if (int64_t(ht) * wd > (int64_t(1) << 24)) return fail_arg(ctx, "ht*wd too large");
+  if (E > 0 && (!targets || !weights || !ii || !jj)) return fail_arg(ctx, "targets / weights / ii / jj must not be NULL");
+  if (!motion_only && E > 0 && (!eta || M <= 0)) return fail_arg(ctx, "eta must not be NULL unless motion_only");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* dba_version(void) { return "libdba 0.1 (sm_100a)"; }
+
+dba_ctx* dba_create(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return nullptr;
+  if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+  dba_ctx* c = new dba_ctx();
+  c->device = device;
+  int cap = 0;
+  cudaDeviceGetAttribute(&cap, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  c->smem_cap = size_t(cap);
+  return c;
+}
+
+void dba_destroy(dba_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+  DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
+                    &c->A, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz};
+  for (DevBuf* b : bufs) b->release();
+  if (c->h_idx) cudaFreeHost(c->h_idx);
+  delete c;
+}
+
+const char* dba_last_error(dba_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int dba_set_option(dba_ctx* ctx, const char* name, double value) {
+  if (!ctx || !name) return -1;
+  std::string n(name);
+  if (n == "block_diag_quirk") ctx->block_diag_quirk = value != 0;
+  else if (n == "keep_system") ctx->keep_system = value != 0;
+  else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
+  else if (n == "ppl") {
+    int v = int(value);
+    if (!(v == 0 || v == 1 || v == 2 || v == 4 || v == 8)) return fail_arg(ctx, "ppl must be 0,1,2,4,8");
+    ctx->opt_ppl = v; ctx->plan_valid = false;
+  } else return fail_arg(ctx, "unknown option " + n);
+  return 0;
+}
+
+int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+           const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+           int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+           int motion_only, float* dx_out, float* dz_out, void* stream) {
+  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, iterations,
+                        motion_only);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  // edge lists -> host (pinned staging), one synchronisation per call
+  if (size_t(2 * E) > ctx->h_idx_cap) {
+    if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
+    ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
+    CK(cudaMallocHost(&ctx->h_idx, size_t(2 * E + 64) * sizeof(int64_t)), "pinned staging");
+    ctx->h_idx_cap = size_t(2 * E + 64);
+  }
+  if (E > 0) {
+    CK(cudaMemcpyAsync(ctx->h_idx, ii, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "ii -> host");
+    CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
+    CK(cudaStreamSynchronize(st), "ii/jj -> host");
+  }
+  return run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ctx->h_idx, ctx->h_idx + E, E, N, ht,
+                wd, M, t0, t1, iterations, lm, ep, motion_only != 0, dx_out, dz_out, st);
+}
+
+int dba_ba_host(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+                int motion_only, float* dx_out, float* dz_out, void* stream) {
+  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, iterations,
+                        motion_only);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  if (t1 - t0 <= 0 || t0 < 0 || t1 > N) return fail_arg(ctx, "need 0 <= t0 < t1 <= N");
+  const size_t HW = size_t(ht) * wd, f = sizeof(float);
+  const size_t Mrows = motion_only ? 0 : size_t(M);
+  CK(ctx->s_poses.ensure(N * 7 * f), "staging"); CK(ctx->s_disps.ensure(N * HW * f), "staging");
+  CK(ctx->s_intr.ensure(4 * f), "staging");
+  CK(ctx->s_targets.ensure(size_t(E) * 2 * HW * f + 16), "staging");
+  CK(ctx->s_weights.ensure(size_t(E) * 2 * HW * f + 16), "staging");
+  CK(ctx->s_eta.ensure(Mrows * HW * f + 16), "staging");
+  CK(ctx->s_dx.ensure(size_t(t1 - t0) * 6 * f), "staging"); CK(ctx->s_dz.ensure(Mrows * HW * f + 16), "staging");
+  if (disps_sens) CK(ctx->s_sens.ensure(N * HW * f), "staging");
+  auto h2d = [&](DevBuf& b, const void* src, size_t bytes) {
+    return bytes ? cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+  };
+  CK(h2d(ctx->s_poses, poses, N * 7 * f), "h2d"); CK(h2d(ctx->s_disps, disps, N * HW * f), "h2d");
+  CK(h2d(ctx->s_intr, intrinsics, 4 * f), "h2d");
+  CK(h2d(ctx->s_targets, targets, size_t(E) * 2 * HW * f), "h2d");
+  CK(h2d(ctx->s_weights, weights, size_t(E) * 2 * HW * f), "h2d");
+  if (Mrows) CK(h2d(ctx->s_eta, eta, Mrows * HW * f), "h2d");
+  if (disps_sens) CK(h2d(ctx->s_sens, disps_sens, N * HW * f), "h2d");
+  rc = run_ba(ctx, ctx->s_poses.as<float>(), ctx->s_disps.as<float>(), ctx->s_intr.as<float>(),
+              disps_sens ? ctx->s_sens.as<float>() : nullptr, ctx->s_targets.as<float>(), ctx->s_weights.as<float>(),
+              ctx->s_eta.as<float>(), ii, jj, E, N, ht, wd, M, t0, t1, iterations, lm, ep, motion_only != 0,
+              dx_out ? ctx->s_dx.as<float>() : nullptr, (dz_out && Mrows) ? ctx->s_dz.as<float>() : nullptr, st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(poses, ctx->s_poses.p, N * 7 * f, cudaMemcpyDeviceToHost, st), "d2h");
+  CK(cudaMemcpyAsync(disps, ctx->s_disps.p, N * HW * f, cudaMemcpyDeviceToHost, st), "d2h");
+  if (dx_out) CK(cudaMemcpyAsync(dx_out, ctx->s_dx.p, size_t(t1 - t0) * 6 * f, cudaMemcpyDeviceToHost, st), "d2h");
+  if (dz_out && Mrows) CK(cudaMemcpyAsync(dz_out, ctx->s_dz.p, Mrows * HW * f, cudaMemcpyDeviceToHost, st), "d2h");
+  CK(cudaStreamSynchronize(st), "d2h");
+  return 0;
+}
+
+int dba_frame_distance(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                       const int64_t* ii, const int64_t* jj, int64_t K, int64_t N, int ht, int wd, float beta,
+                       float* out, void* stream) {
+  if (!ctx) return -1;
+  if (K < 0 || N <= 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (K == 0) return 0;
+  if (!poses || !disps || !intrinsics || !ii || !jj || !out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_frame_distance(poses, disps, intrinsics, ii, jj, K, int(N), ht, wd, beta, out,
+                           reinterpret_cast<cudaStream_t>(stream)), "frame_distance");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_iproj(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, int64_t K, int ht,
+              int wd, float* out, void* stream) {
+  if (!ctx) return -1;
+  if (K < 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (K == 0) return 0;
+  if (!poses || !disps || !intrinsics || !out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_iproj(poses, disps, intrinsics, K, ht, wd, out, reinterpret_cast<cudaStream_t>(stream)), "iproj");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_depth_filter(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                     const int64_t* ix, const float* thresh, int64_t K, int64_t N, int ht, int wd, float* out,
+                     void* stream) {
+  if (!ctx) return -1;
+  if (K < 0 || N <= 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (K == 0) return 0;
+  if (!poses || !disps || !intrinsics || !ix || !thresh || !out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_depth_filter(poses, disps, intrinsics, ix, thresh, K, int(N), ht, wd, out,
+                         reinterpret_cast<cudaStream_t>(stream)), "depth_filter");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_nccl_unique_id(void* out128) {
+  std::string err;
+  if (!out128 || !load_nccl(err)) return -1;
+  int r = g_nccl.GetUniqueId(out128);
+  return r == 0 ? 0 : 1000 + r;
+}
+
+int dba_comm_init(dba_ctx* ctx, int nranks, int rank, const void* id128) {
+  if (!ctx) return -1;
+  if (nranks < 1 || rank < 0 || rank >= nranks || !id128) return fail_arg(ctx, "bad nranks / rank / id");
+  if (!load_nccl(ctx->err)) return -1;
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  if (ctx->comm) { g_nccl.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+  Id128 id;
+  std::memcpy(id.b, id128, 128);
+  int r = g_nccl.CommInitRank(&ctx->comm, nranks, id, rank);
+  if (r != 0) {
+    ctx->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    return 1000 + r;
+  }
+  ctx->nranks = nranks; ctx->rank = rank;
+  return 0;
+}
+
+int dba_comm_destroy(dba_ctx* ctx) {
+  if (!ctx) return -1;
+  if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  ctx->comm = nullptr; ctx->nranks = 1; ctx->rank = 0;
+  return 0;
+}
+
+int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t cap) {
+  if (!ctx || !name || !host_out) return -1;
+  std::string n(name);
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  if (n == "dims") {
+    int32_t d[8] = {ctx->plan.n6, (ctx->plan.n6 + 1 + 3) & ~3, ctx->plan.Pp, ctx->plan.M, ctx->plan.S, ctx->plan_ppl,
+                    ctx->plan.degmax, ctx->plan.npairs_max};
+    if (cap < int64_t(sizeof(d))) return -1;
+    std::memcpy(host_out, d, sizeof(d));
+    return sizeof(d);
+  }
+  if (n == "system") {
+    if (!ctx->keep_system || !ctx->Akeep.p) return fail_arg(ctx, "keep_system option is off");
+    const int ld = (ctx->plan.n6 + 1 + 3) & ~3;
+    int64_t bytes = int64_t(ctx->plan.n6 + 1) * ld * sizeof(float);
+    if (cap < bytes) return -1;
+    if (cudaMemcpy(host_out, ctx->Akeep.p, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return bytes;
+  }
+  return fail_arg(ctx, "unknown debug buffer " + n);
+}
+
+int64_t dba_last_launch_count(dba_ctx* ctx) { return ctx ? ctx->last_launches : -1; }
+
+}  // extern "C"
+
+// ---- host-only plan inspection (tests: the gather lists are checked on the CPU against the oracle's
+// scatter-adds without a GPU) ---------------------------------------------------------------------
+extern "C" {
+
+void* dba_plan_build(const int64_t* ii, const int64_t* jj, int64_t E, int N, int t0, int t1, int motion_only,
+                     int64_t M_expected, int splits, char* err, int errcap) {
+  Plan* P = new Plan();
+  if (!build_plan(*P, ii, jj, E, N, t0, t1, motion_only != 0, M_expected, splits)) {
+    if (err && errcap > 0) { std::strncpy(err, P->error.c_str(), errcap - 1); err[errcap - 1] = 0; }
+    delete P;
+    return nullptr;
+  }
+  return P;
+}
+
+void dba_plan_free(void* plan) { delete reinterpret_cast<Plan*>(plan); }
+
+// copies the named int32 array into out (cap entries); returns its length, or -1
+int64_t dba_plan_get(void* plan, const char* name, int32_t* out, int64_t cap) {
+  if (!plan || !name) return -1;
+  const Plan& P = *reinterpret_cast<Plan*>(plan);
+  std::string n(name);
+  std::vector<int32_t> tmp;
+  const std::vector<int32_t>* v = nullptr;
+  if (n == "kx") v = &P.kx; else if (n == "koff") v = &P.koff; else if (n == "cedge") v = &P.cedge;
+  else if (n == "ci") v = &P.ci; else if (n == "cj") v = &P.cj; else if (n == "pairbase") v = &P.pairbase;
+  else if (n == "blkbase") v = &P.blkbase; else if (n == "sblk_off") v = &P.sblk_off; else if (n == "rhs_off") v = &P.rhs_off;
+  else if (n == "sblk_items" || n == "rhs_items") {
+    const std::vector<Item>& it = (n == "sblk_items") ? P.sblk_items : P.rhs_items;
+    for (const Item& i : it) { tmp.push_back(i.flags); tmp.push_back(i.base); tmp.push_back(i.stride); tmp.push_back(i.pad); }
+    v = &tmp;
+  } else if (n == "dims") {
+    tmp = {P.E, P.N, P.t0, P.t1, P.Pp, P.M, P.n6, P.S, P.degmax, P.nblkmax, P.npairs_max, P.nSblk,
+           int32_t(P.slab_blocks), int32_t(P.vE_blocks)};
+    v = &tmp;
+  } else return -1;
+  if (out && cap >= int64_t(v->size())) std::memcpy(out, v->data(), v->size() * sizeof(int32_t));
+  return int64_t(v->size());
+}
+
+}  // extern "C"

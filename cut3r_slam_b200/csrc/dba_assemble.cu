@@ -1,0 +1,284 @@
+// Assembly of the reduced pose system from the per-CTA partial sums (fixed-order gathers, no
+// atomics), back-substitution of the disparity update and the retractions.
+//
+// Reference maths: hislam2/geom/ba.py:54-59 (Hii,Hij,Hji,Hjj,vi,vj), :70-92 (scatter into H,v;
+// C += eta + 1e-7), chol.py:55-57 (true-diagonal LM damping), :63-64 (S = H - E Q E^T,
+// v' = v - E Q w), :70 (dz = Q (w - E^T dx)), ba.py:101-105 (retractions + disparity guards).
+#include "dba_kernels.h"
+#include "dba_math.cuh"
+#include "dba_plan.h"
+
+namespace dba {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// per edge: sum the split partials of Hjj / vj, expand to the four 6x6 blocks with the adjoint
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci, const int32_t* __restrict__ cj,
+                const float* __restrict__ Hpart, int E, int S, float* __restrict__ Hblk, float* __restrict__ vblk) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= E) return;
+  float hs[27];
+#pragma unroll
+  for (int i = 0; i < 27; ++i) hs[i] = 0.f;
+  for (int s = 0; s < S; ++s) {
+    const float* src = Hpart + (int64_t(c) * S + s) * 32;
+#pragma unroll
+    for (int i = 0; i < 27; ++i) hs[i] += src[i];
+  }
+  float H[36], Ad[36], Rt[12];
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int cc = 0; cc <= r; ++cc) { H[r * 6 + cc] = hs[r * (r + 1) / 2 + cc]; H[cc * 6 + r] = H[r * 6 + cc]; }
+  relative_pose_Rt(poses, ci[c], cj[c], Rt);
+  adjoint_from_Rt(Rt, Ad);
+  float* out = Hblk + int64_t(c) * 144;
+  float Hij[36];   // -Ad^T Hjj
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int cc = 0; cc < 6; ++cc) {
+      float a = 0.f;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) a += Ad[t * 6 + r] * H[t * 6 + cc];
+      Hij[r * 6 + cc] = -a;
+    }
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int cc = 0; cc < 6; ++cc) {
+      float hii = 0.f, hji = 0.f;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) {
+        hii += Hij[r * 6 + t] * Ad[t * 6 + cc];     // (-Ad^T H)(Ad) -> negate below
+        hji += H[r * 6 + t] * Ad[t * 6 + cc];
+      }
+      out[0 * 36 + r * 6 + cc] = -hii;              // Hii = Ad^T Hjj Ad
+      out[1 * 36 + r * 6 + cc] = Hij[r * 6 + cc];   // Hij
+      out[2 * 36 + r * 6 + cc] = -hji;              // Hji = -Hjj Ad
+      out[3 * 36 + r * 6 + cc] = H[r * 6 + cc];     // Hjj
+    }
+  float* vo = vblk + int64_t(c) * 12;
+#pragma unroll
+  for (int r = 0; r < 6; ++r) {
+    float a = 0.f;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) a += Ad[t * 6 + r] * hs[21 + t];
+    vo[r] = -a;                 // vi = -Ad^T vj
+    vo[6 + r] = hs[21 + r];     // vj
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// S (lower block triangle) = damp(sum H) - sum Schur ; 36 threads per 6x6 block, 8 blocks per CTA
+// ---------------------------------------------------------------------------------------------
+constexpr int ASM_BLOCKS = 8;
+
+__global__ void __launch_bounds__(36 * ASM_BLOCKS)
+k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ Hblk,
+             const float* __restrict__ Spart, int S, int nSblk, float lm, float ep, bool block_diag_quirk,
+             float* __restrict__ A, int ldA) {
+  const int ob = blockIdx.x * ASM_BLOCKS + threadIdx.x / 36;
+  const int ent = threadIdx.x % 36;
+  if (ob >= nSblk) return;
+  const int r = ent / 6, c = ent % 6;
+  // ob = a(a+1)/2 + b
+  int a = int((sqrtf(8.0f * float(ob) + 1.0f) - 1.0f) * 0.5f);
+  while ((a + 1) * (a + 2) / 2 <= ob) ++a;
+  while (a * (a + 1) / 2 > ob) --a;
+  const int b = ob - a * (a + 1) / 2;
+  float hsum = 0.f, ssum = 0.f;
+  const int i0 = off[ob], i1 = off[ob + 1];
+  for (int i = i0; i < i1; ++i) {
+    const Item it = items[i];
+    const int e = (it.flags & 2) ? (c * 6 + r) : ent;
+    if ((it.flags & 1) == 0) {
+      hsum += Hblk[int64_t(it.base) * 36 + e];
+    } else {
+      const float* src = Spart + int64_t(it.base) * 36 + e;
+      float t = 0.f;
+      for (int s = 0; s < S; ++s) t += src[int64_t(s) * it.stride * 36];
+      ssum += t;
+    }
+  }
+  // chol.py:55-57: H + (ep + lm H) on the true diagonal; chol.py:35-37 (block_solve as written):
+  // on the diagonal of EVERY 6x6 block when the quirk is requested (motion_only parity switch)
+  const bool damp = (r == c) && (a == b || block_diag_quirk);
+  float val = damp ? hsum + (ep + lm * hsum) : hsum;
+  val -= ssum;
+  A[int64_t(6 * a + r) * ldA + 6 * b + c] = val;
+}
+
+// rhs row of the augmented system: v - E Q w
+__global__ void __launch_bounds__(128)
+k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ vblk,
+               const float* __restrict__ vEpart, int S, int Pp, float* __restrict__ A, int ldA) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= Pp * 6) return;
+  const int a = idx / 6, r = idx % 6;
+  float vsum = 0.f, esum = 0.f;
+  for (int i = off[a]; i < off[a + 1]; ++i) {
+    const Item it = items[i];
+    if ((it.flags & 1) == 0) {
+      vsum += vblk[int64_t(it.base) * 6 + r];
+    } else {
+      const float* src = vEpart + int64_t(it.base) * 6 + r;
+      float t = 0.f;
+      for (int s = 0; s < S; ++s) t += src[int64_t(s) * it.stride * 6];
+      esum += t;
+    }
+  }
+  A[int64_t(6 * Pp) * ldA + idx] = vsum - esum;
+}
+
+// ---------------------------------------------------------------------------------------------
+// back-substitution: dz = Q (w - E^T dx), disparity retraction + guards (one thread per pixel)
+//   E_j . dx_j = h . (d tau_j + phi_j x X1) ;  E_i . dx_k = -h . R (d tau_k + phi_k x X0)
+// ---------------------------------------------------------------------------------------------
+constexpr int BS_T = 128;
+constexpr int BS_CHUNK = 64;
+
+__global__ void __launch_bounds__(BS_T)
+k_backsub(const float* __restrict__ poses, float* __restrict__ disps, const float* __restrict__ intr,
+          const float* __restrict__ weights, const int32_t* __restrict__ kx, const int32_t* __restrict__ koff,
+          const int32_t* __restrict__ cedge, const int32_t* __restrict__ cj, const float* __restrict__ Q,
+          const float* __restrict__ wv, const float* __restrict__ dx, float* __restrict__ dz, int HW, int wd,
+          int ntiles, int t0, int Pp) {
+  __shared__ float sRt[BS_CHUNK * 12];
+  __shared__ float sdx[BS_CHUNK * 6];
+  __shared__ int sedge[BS_CHUNK];
+  const int m = blockIdx.x / ntiles, tile = blockIdx.x % ntiles;
+  const int tid = threadIdx.x;
+  const int k = kx[m];
+  const int e0 = koff[m], deg = koff[m + 1] - e0;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int p = tile * BS_T + tid;
+  const bool inb = p < HW;
+  const float dd = inb ? disps[int64_t(k) * HW + p] : 0.f;
+  const int py = p / wd, px = p - py * wd;
+  const float xx = (float(px) - cx) / fx, yy = (float(py) - cy) / fy;
+  float tk[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (k - t0 >= 0 && k - t0 < Pp) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) tk[i] = dx[(k - t0) * 6 + i];
+  }
+  // z = d tau_k + phi_k x X0
+  const float zx = dd * tk[0] + (tk[4] * 1.f - tk[5] * yy);
+  const float zy = dd * tk[1] + (tk[5] * xx - tk[3] * 1.f);
+  const float zz = dd * tk[2] + (tk[3] * yy - tk[4] * xx);
+  float etdx = 0.f;
+  for (int c0 = 0; c0 < deg; c0 += BS_CHUNK) {
+    const int nc = min(BS_CHUNK, deg - c0);
+    __syncthreads();
+    for (int le = tid; le < nc; le += BS_T) {
+      const int j = cj[e0 + c0 + le];
+      relative_pose_Rt(poses, k, j, sRt + 12 * le);
+      const bool opt = (j - t0 >= 0 && j - t0 < Pp);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) sdx[le * 6 + i] = opt ? dx[(j - t0) * 6 + i] : 0.f;
+      sedge[le] = cedge[e0 + c0 + le];
+    }
+    __syncthreads();
+    if (inb) {
+      for (int le = 0; le < nc; ++le) {
+        const float* Rt = sRt + 12 * le;
+        const float* tj = sdx + 6 * le;
+        const float* wg = weights + int64_t(sedge[le]) * 2 * HW;
+        const float wx = __ldcs(wg + p), wy = __ldcs(wg + HW + p);
+        const Proj pr = project(Rt, xx, yy, dd, fx, fy, cx, cy);
+        const float a0 = kWeightScale * (pr.valid * wx) * pr.jz0, a1 = kWeightScale * (pr.valid * wy) * pr.jz1;
+        const float hx = a0 * pr.a0, hy = a1 * pr.b1, hz = a0 * pr.c0 + a1 * pr.c1;
+        const float X = pr.X1.x, Y = pr.X1.y, Z = pr.X1.z;
+        // u = d tau_j + phi_j x X1 - R z
+        const float ux = dd * tj[0] + (tj[4] * Z - tj[5] * Y) - (Rt[0] * zx + Rt[1] * zy + Rt[2] * zz);
+        const float uy = dd * tj[1] + (tj[5] * X - tj[3] * Z) - (Rt[3] * zx + Rt[4] * zy + Rt[5] * zz);
+        const float uz = dd * tj[2] + (tj[3] * Y - tj[4] * X) - (Rt[6] * zx + Rt[7] * zy + Rt[8] * zz);
+        etdx += hx * ux + hy * uy + hz * uz;
+      }
+    }
+  }
+  if (inb) {
+    const float q = Q[int64_t(m) * HW + p], w = wv[int64_t(m) * HW + p];
+    const float dzv = q * (w - etdx);
+    dz[int64_t(m) * HW + p] = dzv;
+    float nd = dd + dzv;                        // ba.py:102
+    nd = (nd > 10.f) ? 0.f : nd;                // ba.py:104
+    nd = fmaxf(nd, 0.001f);                     // ba.py:105  (NaN -> 0.001, as torch.clamp does not: see DESIGN)
+    disps[int64_t(k) * HW + p] = nd;
+  }
+}
+
+// disparity guards on the frames of [0,t1) that are not a source keyframe (ba.py:104-105 run over
+// the whole slice)
+__global__ void __launch_bounds__(256)
+k_guard(float* __restrict__ disps, const int32_t* __restrict__ frames, int HW) {
+  const int f = frames[blockIdx.y];
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
+    float v = disps[int64_t(f) * HW + p];
+    float nd = (v > 10.f) ? 0.f : v;
+    nd = fmaxf(nd, 0.001f);
+    if (nd != v) disps[int64_t(f) * HW + p] = nd;
+  }
+}
+
+__global__ void __launch_bounds__(128)
+k_retract(float* __restrict__ poses, const float* __restrict__ dx, int t0, int Pp, float* __restrict__ dx_out) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= Pp) return;
+  float xi[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) xi[i] = dx[a * 6 + i];
+  se3_retract(poses + 7 * (t0 + a), xi);
+  if (dx_out != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dx_out[a * 6 + i] = xi[i];
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float lm, float ep,
+                            float /*hscale_lm*/, bool motion_only, bool block_diag_quirk, cudaStream_t st) {
+  (void)motion_only;
+  if (g.E > 0) {
+    k_edge_finalize<<<(g.E + 127) / 128, 128, 0, st>>>(in.poses, g.ci, g.cj, ws.Hpart, g.E, g.S, ws.Hblk, ws.vblk);
+    g_launch_count++;
+  }
+  k_assemble_S<<<(g.nSblk + ASM_BLOCKS - 1) / ASM_BLOCKS, 36 * ASM_BLOCKS, 0, st>>>(
+      g.sblk_off, g.sblk_items, ws.Hblk, ws.Spart, g.S, g.nSblk, lm, ep, block_diag_quirk, ws.A, ws.ldA);
+  k_assemble_rhs<<<(g.Pp * 6 + 127) / 128, 128, 0, st>>>(g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.S, g.Pp,
+                                                         ws.A, ws.ldA);
+  g_launch_count += 2;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_backsub(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, cudaStream_t st) {
+  const int ntiles = (g.HW + BS_T - 1) / BS_T;
+  if (g.M > 0) {
+    g_launch_count++;
+    k_backsub<<<g.M * ntiles, BS_T, 0, st>>>(in.poses, in.disps, in.intrinsics, in.weights, g.kx, g.koff, g.cedge,
+                                             g.cj, ws.Q, ws.w, ws.dx, ws.dz, g.HW, g.wd, ntiles, g.t0, g.Pp);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_guard_nonsrc(const DeviceGraph& g, const BAInputs& in, cudaStream_t st) {
+  if (g.n_nonsrc > 0) {
+    dim3 grid((g.HW + 255) / 256, g.n_nonsrc);
+    k_guard<<<grid, 256, 0, st>>>(in.disps, g.nonsrc, g.HW);
+    g_launch_count++;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* dx_out,
+                           cudaStream_t st) {
+  k_retract<<<(g.Pp + 127) / 128, 128, 0, st>>>(in.poses, ws.dx, g.t0, g.Pp, dx_out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+}  // namespace dba

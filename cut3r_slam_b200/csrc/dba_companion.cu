@@ -1,0 +1,171 @@
+// Companion ops of the `droid_backends` interface: frame_distance, iproj, depth_filter.
+//
+// The reference's CUDA for these (src/droid_kernels.cu) is absent from its tree, so their exact
+// constants are PARITY UNPINNED; the definitions implemented here are the ones documented in
+// DESIGN.md ("Companion ops") and restated on the CPU in oracle/dba.py, built from
+// hislam2/geom/projective_ops.py:44-62 and the call sites depth_video.pyc distance@195-205,
+// hislam2/util/droid_visualization.py:97,100-101.
+#include "dba_kernels.h"
+#include "dba_math.cuh"
+
+namespace dba {
+
+namespace {
+
+constexpr float kFrameDistanceSentinel = 1000.0f;
+constexpr int kDepthFilterRadius = 3;
+
+__global__ void __launch_bounds__(256)
+k_frame_distance(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                 const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int N, int HW, int wd, float beta,
+                 float* __restrict__ out) {
+  __shared__ float sRt[12];
+  __shared__ float sred[2][8];
+  const int pair = blockIdx.x;
+  const int64_t i = ii[pair], j = jj[pair];
+  const bool ok = i >= 0 && i < N && j >= 0 && j < N;
+  if (threadIdx.x == 0 && ok) relative_pose_Rt(poses, int(i), int(j), sRt);
+  __syncthreads();
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  float num = 0.f, den = 0.f;
+  if (ok) {
+    float Rt[12];
+#pragma unroll
+    for (int t = 0; t < 12; ++t) Rt[t] = sRt[t];
+    for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+      const float d = disps[i * HW + p];
+      const int py = p / wd, px = p - py * wd;
+      const float xf = float(px), yf = float(py);
+      const float x0 = (xf - cx) / fx, y0 = (yf - cy) / fy;
+      // full relative motion
+      float X = Rt[0] * x0 + Rt[1] * y0 + Rt[2] + Rt[9] * d;
+      float Y = Rt[3] * x0 + Rt[4] * y0 + Rt[5] + Rt[10] * d;
+      float Z = Rt[6] * x0 + Rt[7] * y0 + Rt[8] + Rt[11] * d;
+      float v1 = Z > kMinDepth ? 1.f : 0.f;
+      float Zs = Z > kMinDepth ? Z : 1.f;
+      float du = fx * (X / Zs) + cx - xf, dv = fy * (Y / Zs) + cy - yf;
+      const float f1 = sqrtf(du * du + dv * dv) * v1;
+      // translation only
+      X = x0 + Rt[9] * d; Y = y0 + Rt[10] * d; Z = 1.f + Rt[11] * d;
+      float v2 = Z > kMinDepth ? 1.f : 0.f;
+      Zs = Z > kMinDepth ? Z : 1.f;
+      du = fx * (X / Zs) + cx - xf; dv = fy * (Y / Zs) + cy - yf;
+      const float f2 = sqrtf(du * du + dv * dv) * v2;
+      num += beta * f1 + (1.f - beta) * f2;
+      den += beta * v1 + (1.f - beta) * v2;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    num += __shfl_xor_sync(0xffffffffu, num, o);
+    den += __shfl_xor_sync(0xffffffffu, den, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { sred[0][warp] = num; sred[1][warp] = den; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float n = 0.f, dn = 0.f;
+    for (int w = 0; w < 8; ++w) { n += sred[0][w]; dn += sred[1][w]; }
+    out[pair] = (!ok || dn < 1.0f) ? kFrameDistanceSentinel : n / fmaxf(dn, 1e-12f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_iproj(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr, int HW,
+        int wd, float* __restrict__ out) {
+  const int k = blockIdx.y;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= HW) return;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const SE3 g = se3_load(poses + 7 * k);
+  const float d = disps[int64_t(k) * HW + p];
+  const int py = p / wd, px = p - py * wd;
+  V3 pt{((float(px) - cx) / fx) / d, ((float(py) - cy) / fy) / d, 1.0f / d};
+  V3 r = qrot(g.q, pt);
+  float* o = out + (int64_t(k) * HW + p) * 3;
+  o[0] = r.x + g.t.x; o[1] = r.y + g.t.y; o[2] = r.z + g.t.z;
+}
+
+__global__ void __launch_bounds__(256)
+k_depth_filter(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+               const int64_t* __restrict__ ix, const float* __restrict__ thresh, int N, int ht, int wd,
+               float* __restrict__ out) {
+  __shared__ float sRt[2 * kDepthFilterRadius][12];
+  __shared__ int sj[2 * kDepthFilterRadius];
+  const int k = blockIdx.y;
+  const int HW = ht * wd;
+  const int64_t i = ix[k];
+  const bool ok = i >= 0 && i < N;
+  if (threadIdx.x < 2 * kDepthFilterRadius) {
+    const int t = threadIdx.x;
+    const int off = (t < kDepthFilterRadius) ? t - kDepthFilterRadius : t - kDepthFilterRadius + 1;
+    const int64_t j = i + off;
+    const bool in = ok && j >= 0 && j < N;
+    sj[t] = in ? int(j) : -1;
+    if (in) relative_pose_Rt(poses, int(i), int(j), sRt[t]);
+  }
+  __syncthreads();
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= HW) return;
+  float cnt = 0.f;
+  if (ok) {
+    const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+    const float th = thresh[k];
+    const float d = disps[i * HW + p];
+    const int py = p / wd, px = p - py * wd;
+    const float x0 = (float(px) - cx) / fx, y0 = (float(py) - cy) / fy;
+    for (int t = 0; t < 2 * kDepthFilterRadius; ++t) {
+      const int j = sj[t];
+      if (j < 0) continue;
+      const float* Rt = sRt[t];
+      const float X = Rt[0] * x0 + Rt[1] * y0 + Rt[2] + Rt[9] * d;
+      const float Y = Rt[3] * x0 + Rt[4] * y0 + Rt[5] + Rt[10] * d;
+      const float Z = Rt[6] * x0 + Rt[7] * y0 + Rt[8] + Rt[11] * d;
+      const bool front = Z > kMinDepth;
+      const float Zs = front ? Z : 1.f;
+      const float uj = fx * (X / Zs) + cx, vj = fy * (Y / Zs) + cy;
+      const float dj = d / Zs;
+      const float u0 = floorf(uj), v0 = floorf(vj);
+      const bool inb = front && u0 >= 0.f && v0 >= 0.f && u0 < float(wd - 1) && v0 < float(ht - 1);
+      if (!inb) continue;
+      const int iu = int(u0), iv = int(v0);
+      const float wx = uj - u0, wy = vj - v0;
+      const float* D = disps + int64_t(j) * HW;
+      const float d00 = D[iv * wd + iu], d01 = D[iv * wd + iu + 1];
+      const float d10 = D[(iv + 1) * wd + iu], d11 = D[(iv + 1) * wd + iu + 1];
+      const float dhat = (1.f - wy) * ((1.f - wx) * d00 + wx * d01) + wy * ((1.f - wx) * d10 + wx * d11);
+      const float err = fabsf(1.0f / fmaxf(dj, 1e-12f) - 1.0f / fmaxf(dhat, 1e-12f));
+      if (dj > 0.f && err < th) cnt += 1.f;
+    }
+  }
+  out[int64_t(k) * HW + p] = cnt;
+}
+
+}  // namespace
+
+cudaError_t launch_frame_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                  const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
+                                  cudaStream_t st) {
+  k_frame_distance<<<unsigned(K), 256, 0, st>>>(poses, disps, intr, ii, jj, N, ht * wd, wd, beta, out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_iproj(const float* poses, const float* disps, const float* intr, int64_t K, int ht, int wd,
+                         float* out, cudaStream_t st) {
+  dim3 grid((ht * wd + 255) / 256, unsigned(K));
+  k_iproj<<<grid, 256, 0, st>>>(poses, disps, intr, ht * wd, wd, out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_depth_filter(const float* poses, const float* disps, const float* intr, const int64_t* ix,
+                                const float* thresh, int64_t K, int N, int ht, int wd, float* out,
+                                cudaStream_t st) {
+  dim3 grid((ht * wd + 255) / 256, unsigned(K));
+  k_depth_filter<<<grid, 256, 0, st>>>(poses, disps, intr, ix, thresh, N, ht, wd, out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+}  // namespace dba

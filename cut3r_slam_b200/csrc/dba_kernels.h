@@ -1,0 +1,75 @@
+// Launchers of the sm_100a DBA kernels (device pointers, one stream, no host synchronisation).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace dba {
+
+struct Item;
+
+// kernels launched since the last reset (per host thread); bench.py reports it as gpu_launches
+extern thread_local int64_t g_launch_count;
+
+// Device-resident view of a Plan (all int32) + workspace pointers for one `ba` call.
+struct DeviceGraph {
+  int E, N, t0, t1, Pp, M, n6, S;
+  int degmax, nblkmax, npairs_max;
+  int HW, ht, wd;
+  const int32_t *kx, *koff, *cedge, *ci, *cj, *pairbase, *blkbase, *nonsrc;
+  int n_nonsrc;
+  const int32_t *sblk_off, *rhs_off;
+  const Item *sblk_items, *rhs_items;
+  int nSblk;
+};
+
+struct BAInputs {
+  float* poses;              // [N,7]   in place
+  float* disps;              // [N,HW]  in place
+  const float* intrinsics;   // [4] device
+  const float* disps_sens;   // [N,HW] or null
+  const float* targets;      // [E,2,HW]
+  const float* weights;      // [E,2,HW]
+  const float* eta;          // [M,HW]
+};
+
+struct Workspace {
+  float* Hpart;    // [E,S,32]
+  float* Spart;    // [slab_blocks,36]
+  float* vEpart;   // [vE_blocks,6]
+  float* Q;        // [M,HW]
+  float* w;        // [M,HW]
+  float* Hblk;     // [E,4,36]
+  float* vblk;     // [E,2,6]
+  float* A;        // [(n6+1), ldA]  reduced system (lower) + rhs row
+  int ldA;
+  float* Ldiag;    // [nkb,32,32] factored diagonal blocks
+  float* dx;       // [Pp,6]
+  float* dz;       // [M,HW]
+  int* fail;       // [1]
+};
+
+// linearisation + Schur products; picks the pixel-tile width from degmax. Returns cudaError_t.
+cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, bool motion_only,
+                             int tiles_per_split, int ppl, cudaStream_t st);
+size_t linearize_smem_bytes(int degmax, int ppl, bool motion_only);
+int linearize_pick_ppl(int degmax, int nblkmax, bool motion_only, int HW, size_t smem_cap);
+
+cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float lm, float ep,
+                            float hscale_lm, bool motion_only, bool block_diag_quirk, cudaStream_t st);
+cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
+cudaError_t launch_backsub(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_guard_nonsrc(const DeviceGraph& g, const BAInputs& in, cudaStream_t st);
+cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* dx_out,
+                           cudaStream_t st);
+
+// companions
+cudaError_t launch_frame_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                  const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
+                                  cudaStream_t st);
+cudaError_t launch_iproj(const float* poses, const float* disps, const float* intr, int64_t K, int ht, int wd,
+                         float* out, cudaStream_t st);
+cudaError_t launch_depth_filter(const float* poses, const float* disps, const float* intr, const int64_t* ix,
+                                const float* thresh, int64_t K, int N, int ht, int wd, float* out,
+                                cudaStream_t st);
+
+}  // namespace dba

@@ -1,0 +1,134 @@
+// Host-side plan construction (see dba_plan.h).  Pure C++, no CUDA.
+#include "dba_plan.h"
+
+#include <algorithm>
+#include <numeric>
+
+namespace dba {
+
+namespace {
+inline int tri(int a, int b) { return a * (a + 1) / 2 + b; }   // a >= b
+
+struct Placed { int32_t dst; Item it; };
+
+// stable counting sort of placements by destination
+void bucket(const std::vector<Placed>& src, int ndst, std::vector<int32_t>& off, std::vector<Item>& items) {
+  off.assign(ndst + 1, 0);
+  for (const auto& p : src) off[p.dst + 1]++;
+  for (int i = 0; i < ndst; ++i) off[i + 1] += off[i];
+  items.resize(src.size());
+  std::vector<int32_t> cur(off.begin(), off.end() - 1);
+  for (const auto& p : src) items[cur[p.dst]++] = p.it;
+}
+}  // namespace
+
+bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int N, int t0, int t1,
+                bool motion_only, int64_t M_expected, int splits) {
+  P = Plan();
+  if (E64 < 0 || E64 > (int64_t(1) << 24)) { P.error = "edge count out of range"; return false; }
+  const int E = int(E64);
+  if (N <= 0 || t0 < 0 || t1 > N || t1 - t0 <= 0) {
+    P.error = "need 0 <= t0 < t1 <= N (number of frames in the pose/disparity buffers)";
+    return false;
+  }
+  for (int e = 0; e < E; ++e) {
+    // the reference slices poses[:t1], disps[:t1] (oracle adapter; ba.py indexes with ii/jj) --
+    // an index outside the slice is an IndexError there and an invalid argument here
+    if (ii[e] < 0 || jj[e] < 0 || ii[e] >= t1 || jj[e] >= t1) {
+      P.error = "edge index outside [0, t1)";
+      return false;
+    }
+  }
+  P.E = E; P.N = N; P.t0 = t0; P.t1 = t1; P.Pp = t1 - t0; P.n6 = 6 * P.Pp; P.S = std::max(1, splits);
+  P.motion_only = motion_only;
+  P.key_ii.assign(ii, ii + E);
+  P.key_jj.assign(jj, jj + E);
+
+  // kx = sorted unique(ii)  (ba.py:70)
+  P.slot_of_frame.assign(N, -1);
+  std::vector<int32_t> deg_of_frame(N, 0);
+  for (int e = 0; e < E; ++e) deg_of_frame[ii[e]]++;
+  for (int f = 0; f < N; ++f)
+    if (deg_of_frame[f] > 0) { P.slot_of_frame[f] = int32_t(P.kx.size()); P.kx.push_back(f); }
+  P.M = int(P.kx.size());
+  if (!motion_only && M_expected >= 0 && M_expected != P.M) {
+    P.error = "eta must hold one map per unique source keyframe (rows of eta != |unique(ii)|)";
+    return false;
+  }
+  // CSR: edges of slot m in ascending edge id
+  P.koff.assign(P.M + 1, 0);
+  for (int m = 0; m < P.M; ++m) P.koff[m + 1] = P.koff[m] + deg_of_frame[P.kx[m]];
+  P.cedge.resize(E); P.ci.resize(E); P.cj.resize(E);
+  {
+    std::vector<int32_t> cur(P.koff.begin(), P.koff.end() - 1);
+    for (int e = 0; e < E; ++e) {
+      int m = P.slot_of_frame[ii[e]];
+      int c = cur[m]++;
+      P.cedge[c] = e; P.ci[c] = int32_t(ii[e]); P.cj[c] = int32_t(jj[e]);
+    }
+  }
+  P.pairbase.assign(P.M + 1, 0);
+  P.blkbase.assign(P.M + 1, 0);
+  for (int m = 0; m < P.M; ++m) {
+    int deg = P.koff[m + 1] - P.koff[m];
+    int nblk = deg + 1;
+    P.degmax = std::max(P.degmax, deg);
+    P.nblkmax = std::max(P.nblkmax, nblk);
+    P.npairs_max = std::max(P.npairs_max, nblk * (nblk + 1) / 2);
+    int64_t pb = int64_t(P.pairbase[m]) + int64_t(nblk) * (nblk + 1) / 2;
+    if (pb * P.S * 36 > (int64_t(1) << 31) - 1) { P.error = "Schur slab exceeds 2^31 floats"; return false; }
+    P.pairbase[m + 1] = int32_t(pb);
+    P.blkbase[m + 1] = P.blkbase[m] + nblk;
+  }
+  P.slab_blocks = motion_only ? 0 : int64_t(P.pairbase[P.M]) * P.S;
+  P.vE_blocks = motion_only ? 0 : int64_t(P.blkbase[P.M]) * P.S;
+  P.nSblk = P.Pp * (P.Pp + 1) / 2;
+
+  // ---- gather lists --------------------------------------------------------------------------
+  std::vector<Placed> sp, rp;
+  sp.reserve(size_t(4) * E + size_t(P.pairbase[P.M]) * 2);
+  rp.reserve(size_t(2) * E + size_t(P.blkbase[P.M]));
+  auto inr = [&](int p) { return p >= 0 && p < P.Pp; };
+  // per-edge blocks (ba.py:73-82,86-88): which = 0 Hii, 1 Hij, 2 Hji, 3 Hjj ; v: 0 vi, 1 vj
+  for (int c = 0; c < E; ++c) {
+    int i = P.ci[c] - t0, j = P.cj[c] - t0;
+    if (inr(i)) {
+      sp.push_back({tri(i, i), Item{0, c * 4 + 0, 0, 0}});
+      rp.push_back({i, Item{0, c * 2 + 0, 0, 0}});
+    }
+    if (inr(j)) {
+      sp.push_back({tri(j, j), Item{0, c * 4 + 3, 0, 0}});
+      rp.push_back({j, Item{0, c * 2 + 1, 0, 0}});
+    }
+    if (inr(i) && inr(j)) {
+      if (i >= j) sp.push_back({tri(i, j), Item{0, c * 4 + 1, 0, 0}});   // Hij at (i,j)
+      if (j >= i) sp.push_back({tri(j, i), Item{0, c * 4 + 2, 0, 0}});   // Hji at (j,i)
+    }
+  }
+  if (!motion_only) {
+    // Schur products (chol.py:63-64): keyframe slot m, panel blocks A >= B
+    for (int m = 0; m < P.M; ++m) {
+      int e0 = P.koff[m], deg = P.koff[m + 1] - e0, nblk = deg + 1;
+      int npairs = nblk * (nblk + 1) / 2;
+      auto pose_of = [&](int b) { return (b == 0 ? P.kx[m] : P.cj[e0 + b - 1]) - t0; };
+      for (int A = 0; A < nblk; ++A) {
+        int pA = pose_of(A);
+        if (!inr(pA)) continue;
+        for (int B = 0; B <= A; ++B) {
+          int pB = pose_of(B);
+          if (!inr(pB)) continue;
+          int32_t base = int32_t(int64_t(P.pairbase[m]) * P.S + tri(A, B));
+          // X = E_A Q E_B^T sits at (pA,pB); X^T at (pB,pA) when A != B
+          if (pA >= pB) sp.push_back({tri(pA, pB), Item{1, base, npairs, 0}});
+          if (A != B && pB >= pA) sp.push_back({tri(pB, pA), Item{1 | 2, base, npairs, 0}});
+        }
+        rp.push_back({pA, Item{1, int32_t(int64_t(P.blkbase[m]) * P.S + A), nblk, 0}});
+      }
+    }
+  }
+  bucket(sp, P.nSblk, P.sblk_off, P.sblk_items);
+  bucket(rp, P.Pp, P.rhs_off, P.rhs_items);
+  return true;
+}
+
+}  // namespace dba

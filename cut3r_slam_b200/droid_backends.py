@@ -1,0 +1,241 @@
+"""Host-side mirror of the reference's `droid_backends` torch extension for the DBA path.
+
+Same function names, argument order and error behaviour as the module the reference builds in
+setup.py:10-30 and calls at depth_video.pyc DepthVideo.cuda_ba@232 (`ba`), distance@195-205
+(`frame_distance`) and hislam2/util/droid_visualization.py:97,100-101 (`iproj`, `depth_filter`):
+CUDA + contiguous tensors or RuntimeError (the CHECK_INPUT convention of
+thirdparty/lietorch/lietorch/extras/extras.cpp:6-8), poses/disps updated in place, work queued on
+the current CUDA stream.  Everything below is argument checking and pointer passing into libdba.so
+(include/dba.h); there is no PyTorch or CPU implementation of any op here.
+
+Use as a drop-in:  `from cut3r_slam_b200 import droid_backends`  (or put it in sys.modules under
+the name `droid_backends`).
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+_ctxs = {}
+
+
+class _Ctx:
+    def __init__(self, device_index):
+        self.lib = _lib.load()
+        self.handle = self.lib.dba_create(device_index)
+        if not self.handle:
+            raise RuntimeError(f"dba_create({device_index}) failed: no such CUDA device")
+        self.device_index = device_index
+
+    def check(self, rc):
+        if rc != 0:
+            msg = self.lib.dba_last_error(self.handle)
+            raise RuntimeError(f"libdba error {rc}: {msg.decode() if msg else ''}")
+
+    def set_option(self, name, value):
+        self.check(self.lib.dba_set_option(self.handle, name.encode(), float(value)))
+
+    def __del__(self):
+        try:
+            if self.handle:
+                self.lib.dba_destroy(self.handle)
+                self.handle = None
+        except Exception:  # interpreter shutdown
+            pass
+
+
+def context(device=None):
+    """The per-device libdba context used by the module-level ops."""
+    if device is None:
+        idx = torch.cuda.current_device()
+    else:
+        dev = torch.device(device)
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    if idx not in _ctxs:
+        _ctxs[idx] = _Ctx(idx)
+    return _ctxs[idx]
+
+
+def set_option(name, value, device=None):
+    """block_diag_quirk / splits / ppl / keep_system (include/dba.h)."""
+    context(device).set_option(name, value)
+
+
+def _check(t, name, dtype, ndim=None, cuda=True):
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError(f"{name} must be a tensor")
+    if cuda and not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if not cuda and t.is_cuda:
+        raise RuntimeError(f"{name} must be a CPU tensor")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    if ndim is not None and t.dim() != ndim:
+        raise RuntimeError(f"{name} must have {ndim} dims, got {tuple(t.shape)}")
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)
+
+
+def _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, motion_only, cuda):
+    _check(poses, "poses", torch.float32, 2, cuda)
+    _check(disps, "disps", torch.float32, 3, cuda)
+    _check(intrinsics, "intrinsics", torch.float32, 1, cuda)
+    _check(targets, "targets", torch.float32, 4, cuda)
+    _check(weights, "weights", torch.float32, 4, cuda)
+    _check(ii, "ii", torch.int64, 1, cuda)
+    _check(jj, "jj", torch.int64, 1, cuda)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if poses.shape[0] != N or poses.shape[1] != 7:
+        raise RuntimeError(f"poses must be [{N},7], got {tuple(poses.shape)}")
+    if intrinsics.numel() != 4:
+        raise RuntimeError("intrinsics must be [4] = fx,fy,cx,cy")
+    if jj.numel() != E:
+        raise RuntimeError("ii and jj must have the same length")
+    for t, nm in ((targets, "targets"), (weights, "weights")):
+        if tuple(t.shape) != (E, 2, ht, wd):
+            raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
+    M = 0
+    if not motion_only:
+        _check(eta, "eta", torch.float32, 3, cuda)
+        if tuple(eta.shape[1:]) != (ht, wd):
+            raise RuntimeError(f"eta must be [M,{ht},{wd}], got {tuple(eta.shape)}")
+        M = eta.shape[0]
+    if disps_sens is not None and disps_sens.numel() > 0:
+        _check(disps_sens, "disps_sens", torch.float32, 3, cuda)
+        if tuple(disps_sens.shape) != (N, ht, wd):
+            raise RuntimeError("disps_sens must have the shape of disps")
+    return N, ht, wd, E, M
+
+
+def ba(*args):
+    """droid_backends.ba -- dense bundle adjustment, in place on poses[t0:t1] and disps[unique(ii)].
+
+    ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm,
+       ep, motion_only)                                   (15 args, BASELINE.json north_star)
+    ba(poses, disps, intrinsics, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+       motion_only)                                       (14 args, depth_video.pyc cuda_ba@232)
+    Returns [dx, dz] of the last iteration (dx [t1-t0,6]; dz [M,ht,wd], empty when motion_only).
+    """
+    if len(args) == 14:
+        args = args[:3] + (None,) + args[3:]
+    if len(args) != 15:
+        raise TypeError(f"ba() takes 14 or 15 positional arguments ({len(args)} given)")
+    (poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+     motion_only) = args
+    motion_only = bool(motion_only)
+    N, ht, wd, E, M = _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, motion_only, True)
+    t0, t1, iterations = int(t0), int(t1), int(iterations)
+    ctx = context(poses.device)
+    dx = torch.zeros((max(t1 - t0, 0), 6), dtype=torch.float32, device=poses.device)
+    dz = torch.zeros((0 if motion_only else M, ht, wd), dtype=torch.float32, device=poses.device)
+    sens = disps_sens if (disps_sens is not None and disps_sens.numel() > 0) else None
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        rc = ctx.lib.dba_ba(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(sens), _ptr(targets),
+                            _ptr(weights), _ptr(eta if not motion_only else None), _ptr(ii), _ptr(jj), E, N, ht, wd,
+                            M, t0, t1, iterations, float(lm), float(ep), int(motion_only), _ptr(dx), _ptr(dz),
+                            C.c_void_p(stream))
+    ctx.check(rc)
+    return [dx, dz]
+
+
+def ba_host(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
+            motion_only, device=None):
+    """Same op on HOST tensors (pinned for full copy speed): copies in, runs, copies poses/disps back.
+    The end-to-end entry point bench.py times (dba_ba_host)."""
+    motion_only = bool(motion_only)
+    N, ht, wd, E, M = _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, motion_only, False)
+    ctx = context(device)
+    dx = torch.zeros((max(int(t1) - int(t0), 0), 6), dtype=torch.float32)
+    sens = disps_sens if (disps_sens is not None and disps_sens.numel() > 0) else None
+    with torch.cuda.device(ctx.device_index):
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = ctx.lib.dba_ba_host(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(sens), _ptr(targets),
+                                 _ptr(weights), _ptr(eta if not motion_only else None), _ptr(ii), _ptr(jj), E, N, ht,
+                                 wd, M, int(t0), int(t1), int(iterations), float(lm), float(ep), int(motion_only),
+                                 _ptr(dx), C.c_void_p(0), C.c_void_p(stream))
+    ctx.check(rc)
+    return [dx]
+
+
+def frame_distance(poses, disps, intrinsics, ii, jj, beta):
+    """droid_backends.frame_distance(poses, disps, intrinsics, ii, jj, beta) -> [K] fp32."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    if ii.numel() != jj.numel():
+        raise RuntimeError("ii and jj must have the same length")
+    N, ht, wd = disps.shape
+    K = ii.numel()
+    out = torch.empty((K,), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_frame_distance(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ii), _ptr(jj),
+                                             K, N, ht, wd, float(beta), _ptr(out), C.c_void_p(stream)))
+    return out
+
+
+def iproj(poses, disps, intrinsics):
+    """droid_backends.iproj(poses_inv, disps, intrinsics) -> [K,ht,wd,3] points G * (X0 / disp)."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    K, ht, wd = disps.shape
+    if poses.shape[0] != K or poses.shape[1] != 7:
+        raise RuntimeError(f"poses must be [{K},7]")
+    out = torch.empty((K, ht, wd, 3), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_iproj(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), K, ht, wd, _ptr(out),
+                                    C.c_void_p(stream)))
+    return out
+
+
+def depth_filter(poses, disps, intrinsics, ix, thresh):
+    """droid_backends.depth_filter(poses, disps, intrinsics, ix, thresh) -> [K,ht,wd] neighbour counts."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ix, "ix", torch.int64, 1)
+    _check(thresh, "thresh", torch.float32, 1)
+    if thresh.numel() != ix.numel():
+        raise RuntimeError("thresh must hold one threshold per entry of ix")
+    N, ht, wd = disps.shape
+    K = ix.numel()
+    out = torch.empty((K, ht, wd), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_depth_filter(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ix),
+                                           _ptr(thresh), K, N, ht, wd, _ptr(out), C.c_void_p(stream)))
+    return out
+
+
+def debug_system(device=None):
+    """(S_lower [n6,n6], rhs [n6]) of the last iteration's reduced system (needs keep_system=1)."""
+    ctx = context(device)
+    dims = (C.c_int32 * 8)()
+    n = ctx.lib.dba_debug_read(ctx.handle, b"dims", dims, C.sizeof(dims))
+    if n < 0:
+        ctx.check(-1)
+    n6, ld = dims[0], dims[1]
+    buf = torch.empty(((n6 + 1), ld), dtype=torch.float32)
+    n = ctx.lib.dba_debug_read(ctx.handle, b"system", C.c_void_p(buf.data_ptr()), buf.numel() * 4)
+    if n < 0:
+        ctx.check(-1)
+    return buf[:n6, :n6].clone(), buf[n6, :n6].clone(), list(dims)
+
+
+def last_launch_count(device=None):
+    ctx = context(device)
+    return int(ctx.lib.dba_last_launch_count(ctx.handle))

@@ -1,0 +1,105 @@
+/* libdba -- B200-native dense bundle adjustment engine: C ABI.
+ *
+ * Drop-in boundary for the `droid_backends` torch extension that the reference builds from
+ * src/droid.cpp + src/droid_kernels.cu (setup.py:10-17; sources absent from the reference tree) and
+ * calls from hislam2 (recovered call sites: depth_video.pyc DepthVideo.cuda_ba@232,
+ * DepthVideo.distance@195-205; live: hislam2/util/droid_visualization.py:97,100-101).
+ * Plain pointers and sizes only; all *device* pointers are CUDA device memory of the context's
+ * device, fp32 unless stated, contiguous.  Every call is asynchronous on `stream` (a cudaStream_t
+ * passed as void*) unless stated; none of them uses the CPU for arithmetic -- there is no fallback.
+ *
+ * Return value: 0 ok; <0 invalid argument (message via dba_last_error); >0 a cudaError_t /
+ * ncclResult_t (+1000) value.
+ */
+#ifndef DBA_H_
+#define DBA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dba_ctx dba_ctx;
+
+/* Context: owns the cached plan (edge CSR + gather lists), the workspace and, for sharded global
+ * BA, the NCCL communicator.  One context per device per caller thread. */
+dba_ctx* dba_create(int device);
+void dba_destroy(dba_ctx* ctx);
+const char* dba_last_error(dba_ctx* ctx);
+const char* dba_version(void);
+
+/* Options (name, value): "block_diag_quirk" 0/1 -- motion_only damping as hislam2/geom/chol.py:35-37
+ * (ep + lm*H on the diagonal of EVERY 6x6 block) instead of the true diagonal (default 0);
+ * "splits" n -- CTAs per source keyframe (0 = auto); "keep_system" 0/1 -- keep a copy of the reduced
+ * system of the last iteration for dba_debug_read; "ppl" n -- pixels per lane override (0 = auto). */
+int dba_set_option(dba_ctx* ctx, const char* name, double value);
+
+/* ---- ba: replaces droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
+ *      ii, jj, t0, t1, iterations, lm, ep, motion_only)  [depth_video.pyc cuda_ba@232; BASELINE.json
+ *      north_star argument list].  Maths: hislam2/geom/ba.py:32-158, chol.py:33-78.
+ *   poses   [N,7]   in/out  [tx,ty,tz,qx,qy,qz,qw] world->camera; frames [t0,t1) are updated
+ *   disps   [N,ht,wd] in/out; rows unique(ii) are updated, guards (>10 -> 0, max(.,1e-3)) on [0,t1)
+ *   intrinsics [4]  device  fx,fy,cx,cy
+ *   disps_sens [N,ht,wd] or NULL (sensor-depth prior; NULL or all <= 0 disables it)
+ *   targets, weights [E,2,ht,wd]
+ *   eta     [M,ht,wd], M = |unique(ii)|, rows in sorted(unique(ii)) order (ignored if motion_only)
+ *   ii, jj  [E] int64 device
+ *   dx_out  [t1-t0,6] or NULL, dz_out [M,ht,wd] or NULL: update of the LAST iteration
+ * Synchronises `stream` once at entry when the edge lists differ from the cached plan's (they are
+ * copied to the host to build the plan); the iteration loop itself never touches the host. */
+int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+           const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+           int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+           int motion_only, float* dx_out, float* dz_out, void* stream);
+
+/* Same, but every buffer is HOST memory (pinned for full speed): inputs are copied to the device,
+ * the iterations run, poses/disps (and dx_out/dz_out if non-NULL) are copied back; returns after
+ * the results are on the host.  This is the end-to-end entry bench.py times. */
+int dba_ba_host(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+                int motion_only, float* dx_out, float* dz_out, void* stream);
+
+/* ---- frame_distance(poses, disps, intrinsics, ii, jj, beta) -> [K]  (depth_video.pyc distance@195-205) */
+int dba_frame_distance(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                       const int64_t* ii, const int64_t* jj, int64_t K, int64_t N, int ht, int wd, float beta,
+                       float* out, void* stream);
+
+/* ---- iproj(poses_inv, disps, intrinsics) -> [K,ht,wd,3]  (hislam2/util/droid_visualization.py:97) */
+int dba_iproj(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, int64_t K, int ht,
+              int wd, float* out, void* stream);
+
+/* ---- depth_filter(poses, disps, intrinsics, ix, thresh) -> [K,ht,wd]  (droid_visualization.py:100-101) */
+int dba_depth_filter(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                     const int64_t* ix, const float* thresh, int64_t K, int64_t N, int ht, int wd, float* out,
+                     void* stream);
+
+/* ---- sharded global BA (no reference counterpart: SURVEY.md section 8e).  Edges are partitioned by
+ * source keyframe ii across ranks; each rank calls dba_ba with ITS edges/targets/weights/eta and a
+ * full replica of poses; the reduced system is summed with one ncclAllReduce per iteration. */
+int dba_nccl_unique_id(void* out128);                                   /* rank 0, then broadcast */
+int dba_comm_init(dba_ctx* ctx, int nranks, int rank, const void* id128);
+int dba_comm_destroy(dba_ctx* ctx);
+
+/* ---- test / profiling hooks */
+/* name: "system" -> [(n6+1)*ld] floats of the last assembled reduced system (needs keep_system=1),
+ * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; returns the number of BYTES
+ * written (<= cap) or <0. Synchronous. */
+int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t cap);
+/* number of kernels launched by the last dba_ba call (for bench.py's gpu_launches) */
+int64_t dba_last_launch_count(dba_ctx* ctx);
+
+/* ---- host-only plan inspection (no GPU needed): the edge CSR and the fixed-order gather lists that
+ * replace the reference's scatter_sum calls (hislam2/geom/ba.py:13-19,73-90).  name: kx, koff, cedge,
+ * ci, cj, pairbase, blkbase, sblk_off, rhs_off, sblk_items, rhs_items (4 int32 per item: flags, base,
+ * stride, 0), dims. */
+void* dba_plan_build(const int64_t* ii, const int64_t* jj, int64_t E, int N, int t0, int t1, int motion_only,
+                     int64_t M_expected, int splits, char* err, int errcap);
+void dba_plan_free(void* plan);
+int64_t dba_plan_get(void* plan, const char* name, int32_t* out, int64_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DBA_H_ */
