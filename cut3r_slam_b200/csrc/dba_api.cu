@@ -79,6 +79,9 @@ struct dba_ctx {
   // options
   bool block_diag_quirk = false;
   bool keep_system = false;
+  bool profile = false;            // CUDA events around every stage (adds a sync at the end of the call)
+  double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // linearize, assemble, allreduce, cholesky, backsub, retract, -, launches
+  std::vector<cudaEvent_t> ev;
   int opt_splits = 0;
   int opt_ppl = 0;
   // plan cache
@@ -242,9 +245,22 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   BAInputs in{poses, disps, intr, disps_sens, targets, weights, eta};
   // sharded: every rank damps its share of H; the constant ep is added once (rank 0)
   const float ep_eff = (ctx->rank == 0) ? ep : 0.f;
+  const bool prof = ctx->profile;
+  size_t nev = 0;
+  if (prof) {
+    while (ctx->ev.size() < size_t(iterations) * 7 + 1) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e), "event");
+      ctx->ev.push_back(e);
+    }
+  }
+  auto mark = [&]() { if (prof) cudaEventRecord(ctx->ev[nev++], st); };
   for (int it = 0; it < iterations; ++it) {
+    mark();
     if (g.E > 0) CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, st), "linearize");
+    mark();
     CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
+    mark();
     if (ctx->comm != nullptr && ctx->nranks > 1) {
       const size_t cnt = size_t(g.n6 + 1) * ws.ldA;
       int r = g_nccl.AllReduce(ws.A, ws.A, cnt, /*ncclFloat32*/ 7, /*ncclSum*/ 0, ctx->comm, st);
@@ -256,9 +272,23 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     if (ctx->keep_system)
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");
+    mark();
     CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
+    mark();
     if (!motion_only && g.E > 0) CK(launch_backsub(g, in, ws, st), "backsub");
+    mark();
     CK(launch_retract(g, in, ws, (it == iterations - 1) ? dx_out : nullptr, st), "retract");
+    mark();
+  }
+  if (prof && nev > 0) {
+    CK(cudaEventSynchronize(ctx->ev[nev - 1]), "profile");
+    for (int it = 0; it < iterations; ++it)
+      for (int k = 0; k < 6; ++k) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ctx->ev[it * 7 + k], ctx->ev[it * 7 + k + 1]);
+        ctx->stage_ms[k] += ms;
+      }
+    ctx->stage_ms[7] += iterations;
   }
   if (!motion_only && iterations > 0) {
     CK(launch_guard_nonsrc(g, in, st), "guard");
@@ -307,6 +337,7 @@ void dba_destroy(dba_ctx* c) {
                     &c->A, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz};
   for (DevBuf* b : bufs) b->release();
+  for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->h_idx) cudaFreeHost(c->h_idx);
   delete c;
 }
@@ -318,6 +349,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   std::string n(name);
   if (n == "block_diag_quirk") ctx->block_diag_quirk = value != 0;
   else if (n == "keep_system") ctx->keep_system = value != 0;
+  else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {
     int v = int(value);
@@ -478,6 +510,11 @@ int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t c
     if (cap < int64_t(sizeof(d))) return -1;
     std::memcpy(host_out, d, sizeof(d));
     return sizeof(d);
+  }
+  if (n == "stage_ms") {
+    if (cap < int64_t(sizeof(ctx->stage_ms))) return -1;
+    std::memcpy(host_out, ctx->stage_ms, sizeof(ctx->stage_ms));
+    return sizeof(ctx->stage_ms);
   }
   if (n == "system") {
     if (!ctx->keep_system || !ctx->Akeep.p) return fail_arg(ctx, "keep_system option is off");

@@ -239,3 +239,16 @@ def debug_system(device=None):
 def last_launch_count(device=None):
     ctx = context(device)
     return int(ctx.lib.dba_last_launch_count(ctx.handle))
+
+
+STAGES = ("linearize", "assemble", "allreduce", "cholesky", "backsub", "retract")
+
+
+def stage_times(device=None):
+    """Per-stage device time accumulated while the "profile" option was on: ({stage: ms}, LM iterations)."""
+    ctx = context(device)
+    buf = (C.c_double * 8)()
+    n = ctx.lib.dba_debug_read(ctx.handle, b"stage_ms", buf, C.sizeof(buf))
+    if n < 0:
+        ctx.check(-1)
+    return {k: buf[i] for i, k in enumerate(STAGES)}, int(buf[7])

@@ -1,0 +1,88 @@
+"""Global BA sharded by source keyframe over the GPUs of one box (no reference
+counterpart -- the reference runs everything on cuda:0).
+
+Every disparity map belongs to exactly one source keyframe k and only edges with ii == k touch it
+(hislam2/geom/ba.py:70,83-90: E, C, w are indexed by kk = inverse(unique(ii))).  So a partition of
+the edges by ii keeps C_k, w_k, E_.k, Q_k, dz_k and disps[k] rank-local; only the reduced pose system
+(H - E Q E^T, v - E Q w) couples the shards, and it is a SUM over k: one ncclAllReduce per LM
+iteration, issued by libdba on the compute stream between assembly and the (replicated) Cholesky.
+The LM damping H_dd (1+lm) + ep is linear in H: every rank damps its share, rank 0 adds ep.
+"""
+import ctypes as C
+
+import torch
+
+from . import droid_backends
+
+
+def partition_by_source(ii, nranks, cost="schur"):
+    """Contiguous ranges of sorted(unique(ii)) per rank, balanced on sum_k (deg_k+1)^2 + 8 deg_k
+    (Schur products + linearisation).  Returns [(keyframes [m_r], edge_index [E_r])] per rank; edge
+    order inside a shard is the original order; eta rows of a shard are the contiguous slice
+    [first_slot, first_slot + m_r) of the global eta."""
+    ii = ii.cpu()
+    kx, kk = torch.unique(ii, return_inverse=True)
+    deg = torch.bincount(kk, minlength=kx.numel()).double()
+    w = (deg + 1) ** 2 + 8 * deg if cost == "schur" else deg
+    cum = torch.cumsum(w, 0)
+    total = float(cum[-1]) if cum.numel() else 0.0
+    bounds = [0]
+    for r in range(1, nranks):
+        target = total * r / nranks
+        b = int(torch.searchsorted(cum, torch.tensor(target, dtype=cum.dtype)))
+        bounds.append(min(max(b, bounds[-1]), kx.numel()))
+    bounds.append(kx.numel())
+    out = []
+    for r in range(nranks):
+        lo, hi = bounds[r], bounds[r + 1]
+        sel = torch.nonzero((kk >= lo) & (kk < hi)).reshape(-1)
+        out.append(dict(slots=(lo, hi), keyframes=kx[lo:hi], edges=sel))
+    return out
+
+
+class ShardedBA:
+    """One instance per rank (process).  `init_comm` wires libdba's NCCL communicator using the
+    existing torch.distributed group only to broadcast the NCCL unique id."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.ctx = droid_backends.context(self.device)
+        self.rank, self.nranks = 0, 1
+
+    def init_comm(self):
+        import torch.distributed as dist
+        self.rank, self.nranks = dist.get_rank(), dist.get_world_size()
+        if self.nranks == 1:
+            return
+        idbuf = (C.c_char * 128)()
+        if self.rank == 0:
+            rc = self.ctx.lib.dba_nccl_unique_id(idbuf)
+            if rc != 0:
+                raise RuntimeError(f"dba_nccl_unique_id failed ({rc})")
+        obj = [bytes(idbuf.raw) if self.rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        idbuf.raw = obj[0]
+        with torch.cuda.device(self.device):
+            self.ctx.check(self.ctx.lib.dba_comm_init(self.ctx.handle, self.nranks, self.rank, idbuf))
+
+    def close(self):
+        self.ctx.lib.dba_comm_destroy(self.ctx.handle)
+
+    def ba(self, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep):
+        """The rank's shard: targets/weights/eta/ii/jj hold ITS edges (global frame indices); poses is
+        a full replica (updated identically on every rank); disps rows of ITS source keyframes are
+        updated, the others are stale until `gather_disps`."""
+        return droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
+                                 iterations, lm, ep, False)
+
+    def gather_disps(self, disps, shards):
+        """Make every rank's disps complete again: each rank broadcasts the rows of its keyframes."""
+        import torch.distributed as dist
+        for r, sh in enumerate(shards):
+            rows = sh["keyframes"].to(disps.device)
+            if rows.numel() == 0:
+                continue
+            buf = disps[rows].contiguous()
+            dist.broadcast(buf, src=r)
+            disps[rows] = buf
+        return disps

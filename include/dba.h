@@ -32,7 +32,9 @@ const char* dba_version(void);
 /* Options (name, value): "block_diag_quirk" 0/1 -- motion_only damping as hislam2/geom/chol.py:35-37
  * (ep + lm*H on the diagonal of EVERY 6x6 block) instead of the true diagonal (default 0);
  * "splits" n -- CTAs per source keyframe (0 = auto); "keep_system" 0/1 -- keep a copy of the reduced
- * system of the last iteration for dba_debug_read; "ppl" n -- pixels per lane override (0 = auto). */
+ * system of the last iteration for dba_debug_read; "ppl" n -- pixels per lane override (0 = auto);
+ * "profile" 0/1 -- bracket every stage with CUDA events on `stream` and accumulate per-stage times
+ * (setting it resets the accumulators; the call then waits for its last event before returning). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
 
 /* ---- ba: replaces droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
@@ -84,7 +86,8 @@ int dba_comm_destroy(dba_ctx* ctx);
 
 /* ---- test / profiling hooks */
 /* name: "system" -> [(n6+1)*ld] floats of the last assembled reduced system (needs keep_system=1),
- * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; returns the number of BYTES
+ * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; "stage_ms" -> double[8] accumulated
+ * {linearize, assemble, allreduce, cholesky+solve, backsub, retract, 0, LM iterations}; returns the number of BYTES
  * written (<= cap) or <0. Synchronous. */
 int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t cap);
 /* number of kernels launched by the last dba_ba call (for bench.py's gpu_launches) */
