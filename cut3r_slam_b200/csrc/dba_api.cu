@@ -91,7 +91,9 @@ struct dba_ctx {
   DevBuf d_plan_i32, d_items;
   DeviceGraph g{};
   // workspace
-  DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Ldiag, dx, dz, fail, Akeep;
+  DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep;
+  int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
+  bool opt_multilaunch_chol = false;
   // host staging
   int64_t* h_idx = nullptr;
   size_t h_idx_cap = 0;
@@ -220,12 +222,14 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
   CK(ctx->A.ensure(size_t(P.n6 + 1) * ld * f, true), "workspace");
   const int nkb = (P.n6 + 31) / 32;
   CK(ctx->Ldiag.ensure(size_t(nkb) * 1024 * f), "workspace");
+  CK(ctx->Lm.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
+  if (ctx->coop_n != P.n6) { ctx->coop_ctas = cholesky_coop_max_ctas(P.n6); ctx->coop_n = P.n6; }
   CK(ctx->dx.ensure(size_t(P.n6) * f + 16), "workspace");
   CK(ctx->fail.ensure(16, true), "workspace");
   if (ctx->keep_system) CK(ctx->Akeep.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
   ws.Hpart = ctx->Hpart.as<float>(); ws.Spart = ctx->Spart.as<float>(); ws.vEpart = ctx->vEpart.as<float>();
   ws.Q = ctx->Q.as<float>(); ws.w = ctx->w.as<float>(); ws.Hblk = ctx->Hblk.as<float>(); ws.vblk = ctx->vblk.as<float>();
-  ws.A = ctx->A.as<float>(); ws.ldA = ld; ws.Ldiag = ctx->Ldiag.as<float>(); ws.dx = ctx->dx.as<float>();
+  ws.A = ctx->A.as<float>(); ws.Lm = ctx->Lm.as<float>(); ws.ldA = ld; ws.Ldiag = ctx->Ldiag.as<float>(); ws.dx = ctx->dx.as<float>();
   ws.dz = ctx->dz.as<float>(); ws.fail = ctx->fail.as<int>();
   return 0;
 }
@@ -273,7 +277,10 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");
     mark();
-    CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
+    if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol)
+      CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st), "cholesky (cooperative)");
+    else
+      CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
     mark();
     if (!motion_only && g.E > 0) CK(launch_backsub(g, in, ws, st), "backsub");
     mark();
@@ -334,7 +341,7 @@ void dba_destroy(dba_ctx* c) {
   cudaSetDevice(c->device);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
-                    &c->A, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
+                    &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -350,6 +357,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   if (n == "block_diag_quirk") ctx->block_diag_quirk = value != 0;
   else if (n == "keep_system") ctx->keep_system = value != 0;
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
+  else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {
     int v = int(value);

@@ -73,17 +73,19 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
 }
 
 // ---------------------------------------------------------------------------------------------
-// S (lower block triangle) = damp(sum H) - sum Schur ; 36 threads per 6x6 block, 8 blocks per CTA
+// S (lower block triangle) = damp(sum H) - sum Schur.  One CTA per 6x6 block: 8 item lanes x 36
+// entries; item lane l gathers items l, l+8, ... and the 8 partials are summed in lane order
+// (fixed order -> reproducible).  Diagonal blocks carry ~50 items, off-diagonal ones a handful.
 // ---------------------------------------------------------------------------------------------
-constexpr int ASM_BLOCKS = 8;
+constexpr int ASM_LANES = 8;
 
-__global__ void __launch_bounds__(36 * ASM_BLOCKS)
+__global__ void __launch_bounds__(36 * ASM_LANES)
 k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ Hblk,
              const float* __restrict__ Spart, int S, int nSblk, float lm, float ep, bool block_diag_quirk,
              float* __restrict__ A, int ldA) {
-  const int ob = blockIdx.x * ASM_BLOCKS + threadIdx.x / 36;
-  const int ent = threadIdx.x % 36;
-  if (ob >= nSblk) return;
+  __shared__ float sh[ASM_LANES][36], ss[ASM_LANES][36];
+  const int ob = blockIdx.x;
+  const int il = threadIdx.x / 36, ent = threadIdx.x % 36;
   const int r = ent / 6, c = ent % 6;
   // ob = a(a+1)/2 + b
   int a = int((sqrtf(8.0f * float(ob) + 1.0f) - 1.0f) * 0.5f);
@@ -92,18 +94,26 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
   const int b = ob - a * (a + 1) / 2;
   float hsum = 0.f, ssum = 0.f;
   const int i0 = off[ob], i1 = off[ob + 1];
-  for (int i = i0; i < i1; ++i) {
+  for (int i = i0 + il; i < i1; i += ASM_LANES) {
     const Item it = items[i];
     const int e = (it.flags & 2) ? (c * 6 + r) : ent;
     if ((it.flags & 1) == 0) {
-      hsum += Hblk[int64_t(it.base) * 36 + e];
+      hsum += __ldcg(Hblk + int64_t(it.base) * 36 + e);
     } else {
       const float* src = Spart + int64_t(it.base) * 36 + e;
+      const int64_t st = int64_t(it.stride) * 36;
       float t = 0.f;
-      for (int s = 0; s < S; ++s) t += src[int64_t(s) * it.stride * 36];
+#pragma unroll 4
+      for (int s = 0; s < S; ++s) t += __ldcg(src + s * st);
       ssum += t;
     }
   }
+  sh[il][ent] = hsum;
+  ss[il][ent] = ssum;
+  __syncthreads();
+  if (il != 0) return;
+#pragma unroll
+  for (int l = 1; l < ASM_LANES; ++l) { hsum += sh[l][ent]; ssum += ss[l][ent]; }
   // chol.py:55-57: H + (ep + lm H) on the true diagonal; chol.py:35-37 (block_solve as written):
   // on the diagonal of EVERY 6x6 block when the quirk is requested (motion_only parity switch)
   const bool damp = (r == c) && (a == b || block_diag_quirk);
@@ -112,26 +122,36 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
   A[int64_t(6 * a + r) * ldA + 6 * b + c] = val;
 }
 
-// rhs row of the augmented system: v - E Q w
-__global__ void __launch_bounds__(128)
+// rhs row of the augmented system: v - E Q w.  One CTA per pose: 16 item lanes x 6 entries.
+constexpr int RHS_LANES = 16;
+
+__global__ void __launch_bounds__(6 * RHS_LANES)
 k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ vblk,
                const float* __restrict__ vEpart, int S, int Pp, float* __restrict__ A, int ldA) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= Pp * 6) return;
-  const int a = idx / 6, r = idx % 6;
+  __shared__ float sv[RHS_LANES][6], se[RHS_LANES][6];
+  const int a = blockIdx.x;
+  const int il = threadIdx.x / 6, r = threadIdx.x % 6;
   float vsum = 0.f, esum = 0.f;
-  for (int i = off[a]; i < off[a + 1]; ++i) {
+  for (int i = off[a] + il; i < off[a + 1]; i += RHS_LANES) {
     const Item it = items[i];
     if ((it.flags & 1) == 0) {
-      vsum += vblk[int64_t(it.base) * 6 + r];
+      vsum += __ldcg(vblk + int64_t(it.base) * 6 + r);
     } else {
       const float* src = vEpart + int64_t(it.base) * 6 + r;
+      const int64_t st = int64_t(it.stride) * 6;
       float t = 0.f;
-      for (int s = 0; s < S; ++s) t += src[int64_t(s) * it.stride * 6];
+#pragma unroll 4
+      for (int s = 0; s < S; ++s) t += __ldcg(src + s * st);
       esum += t;
     }
   }
-  A[int64_t(6 * Pp) * ldA + idx] = vsum - esum;
+  sv[il][r] = vsum;
+  se[il][r] = esum;
+  __syncthreads();
+  if (il != 0) return;
+#pragma unroll
+  for (int l = 1; l < RHS_LANES; ++l) { vsum += sv[l][r]; esum += se[l][r]; }
+  A[int64_t(6 * Pp) * ldA + a * 6 + r] = vsum - esum;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -247,9 +267,9 @@ cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Work
     k_edge_finalize<<<(g.E + 127) / 128, 128, 0, st>>>(in.poses, g.ci, g.cj, ws.Hpart, g.E, g.S, ws.Hblk, ws.vblk);
     g_launch_count++;
   }
-  k_assemble_S<<<(g.nSblk + ASM_BLOCKS - 1) / ASM_BLOCKS, 36 * ASM_BLOCKS, 0, st>>>(
+  k_assemble_S<<<g.nSblk, 36 * ASM_LANES, 0, st>>>(
       g.sblk_off, g.sblk_items, ws.Hblk, ws.Spart, g.S, g.nSblk, lm, ep, block_diag_quirk, ws.A, ws.ldA);
-  k_assemble_rhs<<<(g.Pp * 6 + 127) / 128, 128, 0, st>>>(g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.S, g.Pp,
+  k_assemble_rhs<<<g.Pp, 6 * RHS_LANES, 0, st>>>(g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.S, g.Pp,
                                                          ws.A, ws.ldA);
   g_launch_count += 2;
   return cudaGetLastError();

@@ -42,7 +42,8 @@ struct Workspace {
   float* vblk;     // [E,2,6]
   float* A;        // [(n6+1), ldA]  reduced system (lower) + rhs row
   int ldA;
-  float* Ldiag;    // [nkb,32,32] factored diagonal blocks
+  float* Ldiag;    // [nkb,32,32] diagonal blocks of the factor (multi-launch path) / their inverses (cooperative path)
+  float* Lm;       // [(n6+1), ldA]  the factor's panels + forward-solved rhs row (cooperative path)
   float* dx;       // [Pp,6]
   float* dz;       // [M,HW]
   int* fail;       // [1]
@@ -57,6 +58,9 @@ int linearize_pick_ppl(int degmax, int nblkmax, bool motion_only, int HW, size_t
 cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float lm, float ep,
                             float hscale_lm, bool motion_only, bool block_diag_quirk, cudaStream_t st);
 cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
+// single cooperative launch (one grid barrier per block step); max_ctas from cholesky_coop_max_ctas (0 = unavailable)
+cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st);
+int cholesky_coop_max_ctas(int n6);
 cudaError_t launch_backsub(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_guard_nonsrc(const DeviceGraph& g, const BAInputs& in, cudaStream_t st);
 cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* dx_out,

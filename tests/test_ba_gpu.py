@@ -286,3 +286,21 @@ def test_full_size_properties(name):
     hp = [t.pin_memory() if isinstance(t, torch.Tensor) else t for t in h.ba_args()]
     db.ba_host(*hp)
     assert torch.equal(hp[0], poses) and torch.equal(hp[1], disps)
+
+
+def test_cholesky_paths_agree():
+    """Cooperative single-launch Cholesky (default) vs the multi-launch blocked path."""
+    db = _db()
+    p = make_problem(P=40, E=300, ht=20, wd=24, iters=2, t0=2, r=4, seed=81)      # n6 = 228: 8 block steps
+    a = p.to("cuda")
+    db.ba(*a.ba_args())
+    db.set_option("multilaunch_cholesky", 1)
+    try:
+        b = p.to("cuda")
+        db.ba(*b.ba_args())
+    finally:
+        db.set_option("multilaunch_cholesky", 0)
+    assert rel_err(b.disps.cpu(), a.disps.cpu()) < 2e-4
+    assert float((b.poses - a.poses).abs().max()) < 1e-4
+    ref_p, ref_d = od.oracle_ba(*p.ba_args(), dtype=torch.float64)
+    assert rel_err(a.disps.cpu(), ref_d) < 1e-4
