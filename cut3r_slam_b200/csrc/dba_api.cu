@@ -220,8 +220,7 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
   CK(ctx->vblk.ensure(size_t(P.E) * 12 * f + 16), "workspace");
   const int ld = (P.n6 + 1 + 3) & ~3;
   CK(ctx->A.ensure(size_t(P.n6 + 1) * ld * f, true), "workspace");
-  const int nkb = (P.n6 + 31) / 32;
-  CK(ctx->Ldiag.ensure(size_t(nkb) * 1024 * f), "workspace");
+  CK(ctx->Ldiag.ensure(cholesky_ldiag_floats(P.n6) * f + 16), "workspace");
   CK(ctx->Lm.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
   if (ctx->coop_n != P.n6) { ctx->coop_ctas = cholesky_coop_max_ctas(P.n6); ctx->coop_n = P.n6; }
   CK(ctx->dx.ensure(size_t(P.n6) * f + 16), "workspace");

@@ -42,11 +42,11 @@ struct Workspace {
   float* vblk;     // [E,2,6]
   float* A;        // [(n6+1), ldA]  reduced system (lower) + rhs row
   int ldA;
-  float* Ldiag;    // [nkb,32,32] diagonal blocks of the factor (multi-launch path) / their inverses (cooperative path)
+  float* Ldiag;    // per 32x32 diagonal block of the factor: L^T | 1/diag | L^-1 (cholesky_ldiag_floats)
   float* Lm;       // [(n6+1), ldA]  the factor's panels + forward-solved rhs row (cooperative path)
   float* dx;       // [Pp,6]
   float* dz;       // [M,HW]
-  int* fail;       // [1]
+  int* fail;       // [4]: [0] failed-factorisation flag, [1] grid-barrier counter (both self-resetting)
 };
 
 // linearisation + Schur products; picks the pixel-tile width from degmax. Returns cudaError_t.
@@ -61,6 +61,7 @@ cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
 // single cooperative launch (one grid barrier per block step); max_ctas from cholesky_coop_max_ctas (0 = unavailable)
 cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st);
 int cholesky_coop_max_ctas(int n6);
+size_t cholesky_ldiag_floats(int n6);   // floats in Workspace::Ldiag
 cudaError_t launch_backsub(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_guard_nonsrc(const DeviceGraph& g, const BAInputs& in, cudaStream_t st);
 cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* dx_out,

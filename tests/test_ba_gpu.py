@@ -75,8 +75,16 @@ def test_reduced_system_matches_oracle(kw):
     Sgpu = torch.tril(S.double())
     assert rel_err(Sgpu, Sref) < 2e-5
     assert rel_err(rhs, sol["vs"]) < 2e-5
-    assert rel_err(dz.cpu().reshape(sol["dz"].shape), sol["dz"]) < 2e-3
-    assert rel_err(dx.cpu(), sol["dx"]) < 2e-3
+    # The solve amplifies fp32 rounding by cond(S) (1e4 .. 1e5 on these graphs: rounding S itself to
+    # fp32 already moves dx by ~1e-3 at cond 1e5), so dx / dz are judged like the golden vectors:
+    # against the fp64 answer, within a small multiple of the reference algorithm's own fp32 error.
+    lin32 = od.linearize(p.targets.permute(0, 2, 3, 1), p.weights.permute(0, 2, 3, 1), p.eta, p.poses, p.disps,
+                         p.intrinsics, p.ii, p.jj, p.t0)
+    sol32 = od.schur_solve(lin32["H"], lin32["E"], lin32["C"], lin32["v"], lin32["w"], ep=p.ep, lm=p.lm)
+    gap_dx = rel_err(sol32["dx"], sol["dx"])
+    gap_dz = rel_err(sol32["dz"], sol["dz"])
+    assert rel_err(dx.cpu(), sol["dx"]) < 4 * gap_dx + 1e-5, gap_dx
+    assert rel_err(dz.cpu().reshape(sol["dz"].shape), sol["dz"]) < 4 * gap_dz + 1e-5, gap_dz
 
 
 @pytest.mark.parametrize("name,kw", [
