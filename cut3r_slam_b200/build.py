@@ -14,8 +14,8 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libdba.so")
 STAMP = os.path.join(HERE, "csrc", ".build_stamp")
 
-SOURCES = ["dba_api.cu", "dba_linearize.cu", "dba_assemble.cu", "dba_chol.cu", "dba_chol_fused.cu", "dba_companion.cu", "dba_plan.cpp"]
-HEADERS = ["dba_kernels.h", "dba_math.cuh", "dba_plan.h", os.path.join("..", "..", "include", "dba.h")]
+SOURCES = ["dba_api.cu", "dba_linearize.cu", "dba_linearize_tc.cu", "dba_assemble.cu", "dba_chol.cu", "dba_chol_fused.cu", "dba_companion.cu", "dba_plan.cpp"]
+HEADERS = ["dba_kernels.h", "dba_math.cuh", "dba_linearize.cuh", "dba_umma.cuh", "dba_plan.h", os.path.join("..", "..", "include", "dba.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

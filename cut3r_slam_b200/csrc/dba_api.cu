@@ -6,7 +6,10 @@
 #include <dlfcn.h>
 
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
+#include <functional>
+#include <queue>
 #include <string>
 #include <vector>
 
@@ -94,6 +97,7 @@ struct dba_ctx {
   DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep;
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
+  bool opt_tc = true;                // Schur products on tcgen05 where the out-degree allows
   // host staging
   int64_t* h_idx = nullptr;
   size_t h_idx_cap = 0;
@@ -148,7 +152,18 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   }
   int Mq = 0;
   const int degmax = out_degree_max(ii, E, N, &Mq);
-  int ppl = ctx->opt_ppl > 0 ? ctx->opt_ppl : linearize_pick_ppl(degmax, degmax + 1, motion_only, HW, ctx->smem_cap);
+  // tensor-core path: keyframes with out-degree <= 20; both kernels then share the 64-pixel tiling
+  int n_tc_kf = 0, degmax_tc = 0;
+  if (ctx->opt_tc && !motion_only) {
+    std::vector<int> dg(N, 0);
+    for (int64_t e = 0; e < E; ++e) dg[ii[e]]++;
+    for (int f = 0; f < N; ++f)
+      if (dg[f] > 0 && dg[f] <= linearize_tc_max_degree()) { ++n_tc_kf; if (dg[f] > degmax_tc) degmax_tc = dg[f]; }
+    if (n_tc_kf > 0 && linearize_tc_smem_bytes(degmax_tc) > ctx->smem_cap) n_tc_kf = 0;
+  }
+  const bool use_tc = n_tc_kf > 0;
+  int ppl = use_tc ? linearize_tc_ppl()
+                   : (ctx->opt_ppl > 0 ? ctx->opt_ppl : linearize_pick_ppl(degmax, degmax + 1, motion_only, HW, ctx->smem_cap));
   if (ppl == 0 || linearize_smem_bytes(degmax, ppl, motion_only) > ctx->smem_cap)
     return fail_arg(ctx, "a source keyframe has too many outgoing edges for the shared-memory panel (limit ~200)");
   const int T = 32 * ppl;
@@ -157,7 +172,37 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   if (S <= 0) {
     int sm = 148;
     cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, ctx->device);
-    S = (4 * sm + (Mq > 0 ? Mq : 1) - 1) / (Mq > 0 ? Mq : 1);
+    if (use_tc) {
+      // CTAs are dispatched in block order onto 2 slots per SM: simulate that list schedule for every
+      // split count (jobs = keyframes sorted by out-degree x pixel splits) and keep the shortest
+      std::vector<int> dg(N, 0), degs;
+      for (int64_t e = 0; e < E; ++e) dg[ii[e]]++;
+      for (int f = 0; f < N; ++f)
+        if (dg[f] > 0 && dg[f] <= linearize_tc_max_degree()) degs.push_back(dg[f]);
+      std::sort(degs.begin(), degs.end(), std::greater<int>());
+      const int slots = 2 * sm;
+      double best = 1e300;
+      for (int cand = 1; cand <= 16 && cand <= ntilesT; ++cand) {
+        const int tps_c = (ntilesT + cand - 1) / cand, S_c = (ntilesT + tps_c - 1) / tps_c;
+        if (S_c != cand) continue;
+        std::priority_queue<double, std::vector<double>, std::greater<double>> free_at;
+        for (int i = 0; i < slots; ++i) free_at.push(0.0);
+        double makespan = 0.0;
+        for (int dgk : degs)
+          for (int sp = 0; sp < S_c; ++sp) {
+            const int nt = std::min(tps_c, ntilesT - sp * tps_c);
+            const double t0s = free_at.top();
+            free_at.pop();
+            const double t1s = t0s + 4.0 + nt * (dgk + 6.0);      // fixed prologue/epilogue + per-tile work
+            free_at.push(t1s);
+            if (t1s > makespan) makespan = t1s;
+          }
+        const double score = makespan * (1.0 + 0.01 * S_c);         // partial slabs cost assembly traffic
+        if (score < best) { best = score; S = S_c; }
+      }
+    } else {
+      S = (4 * sm + (Mq > 0 ? Mq : 1) - 1) / (Mq > 0 ? Mq : 1);
+    }
   }
   if (S > ntilesT) S = ntilesT;
   if (S < 1) S = 1;
@@ -166,6 +211,15 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
   ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW;
 
+  // kernel assignment of the source keyframes
+  std::vector<int32_t> tc_list, simt_list;
+  for (int m = 0; m < P.M; ++m) {
+    const int dgm = P.koff[m + 1] - P.koff[m];
+    if (use_tc && dgm <= linearize_tc_max_degree()) tc_list.push_back(m); else simt_list.push_back(m);
+  }
+  auto by_degree = [&](int32_t a, int32_t b) { return (P.koff[a + 1] - P.koff[a]) > (P.koff[b + 1] - P.koff[b]); };
+  std::stable_sort(tc_list.begin(), tc_list.end(), by_degree);       // heavy keyframes are dispatched first
+  std::stable_sort(simt_list.begin(), simt_list.end(), by_degree);
   // non-source frames of [0,t1)
   std::vector<int32_t> nonsrc;
   for (int f = 0; f < t1; ++f) if (P.slot_of_frame[f] < 0) nonsrc.push_back(f);
@@ -180,6 +234,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   };
   size_t o_kx = put(P.kx), o_koff = put(P.koff), o_cedge = put(P.cedge), o_ci = put(P.ci), o_cj = put(P.cj);
   size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
+  size_t o_tc = put(tc_list), o_sl = put(simt_list);
   CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
   CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
   std::vector<Item> items(P.sblk_items);
@@ -199,6 +254,8 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   g.kx = base + o_kx; g.koff = base + o_koff; g.cedge = base + o_cedge; g.ci = base + o_ci; g.cj = base + o_cj;
   g.pairbase = base + o_pb; g.blkbase = base + o_bb; g.nonsrc = base + o_ns; g.n_nonsrc = int(nonsrc.size());
   g.sblk_off = base + o_so; g.rhs_off = base + o_ro;
+  g.tc_list = base + o_tc; g.simt_list = base + o_sl; g.n_tc = int(tc_list.size()); g.n_simt = int(simt_list.size());
+  g.degmax_tc = degmax_tc;
   g.sblk_items = ctx->d_items.as<Item>();
   g.rhs_items = ctx->d_items.as<Item>() + n_s;
   g.nSblk = P.nSblk;
@@ -260,7 +317,12 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   auto mark = [&]() { if (prof) cudaEventRecord(ctx->ev[nev++], st); };
   for (int it = 0; it < iterations; ++it) {
     mark();
-    if (g.E > 0) CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, st), "linearize");
+    if (g.E > 0) {
+      if (g.n_tc > 0)
+        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, st), "linearize (tcgen05)");
+      if (g.n_simt > 0)
+        CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, st), "linearize");
+    }
     mark();
     CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
     mark();
@@ -357,6 +419,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "keep_system") ctx->keep_system = value != 0;
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
+  else if (n == "tensor_cores") { ctx->opt_tc = value != 0; ctx->plan_valid = false; }
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {
     int v = int(value);

@@ -17,6 +17,9 @@ struct DeviceGraph {
   int HW, ht, wd;
   const int32_t *kx, *koff, *cedge, *ci, *cj, *pairbase, *blkbase, *nonsrc;
   int n_nonsrc;
+  // source-keyframe slots by linearisation kernel: tensor-core Schur products (out-degree <= 20) / SIMT
+  const int32_t *tc_list, *simt_list;
+  int n_tc, n_simt, degmax_tc;
   const int32_t *sblk_off, *rhs_off;
   const Item *sblk_items, *rhs_items;
   int nSblk;
@@ -51,7 +54,13 @@ struct Workspace {
 
 // linearisation + Schur products; picks the pixel-tile width from degmax. Returns cudaError_t.
 cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, bool motion_only,
-                             int tiles_per_split, int ppl, cudaStream_t st);
+                             int tiles_per_split, int ppl, const int32_t* kf_list, int nkf, cudaStream_t st);
+// tcgen05 variant (dba_linearize_tc.cu): keyframes of kf_list, all with out-degree <= linearize_tc_max_degree()
+cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
+                                const int32_t* kf_list, int nkf, int degmax, cudaStream_t st);
+size_t linearize_tc_smem_bytes(int degmax);
+int linearize_tc_max_degree();
+int linearize_tc_ppl();
 size_t linearize_smem_bytes(int degmax, int ppl, bool motion_only);
 int linearize_pick_ppl(int degmax, int nblkmax, bool motion_only, int HW, size_t smem_cap);
 

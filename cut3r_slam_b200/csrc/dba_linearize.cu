@@ -10,8 +10,7 @@
 //
 // Maths follows hislam2/geom/ba.py:39-68,83-92 + chol.py:53-64 of the reference in the reduced
 // form proven in tests/test_kernel_algebra.py (Ji/Hii/Hij/Ei are never formed per pixel).
-#include "dba_kernels.h"
-#include "dba_math.cuh"
+#include "dba_linearize.cuh"
 
 namespace dba {
 
@@ -19,14 +18,6 @@ namespace {
 
 constexpr int NT = 256;   // threads per CTA
 constexpr int NW = NT / 32;
-
-struct LinParams {
-  const float* poses; const float* disps; const float* intr; const float* disps_sens;
-  const float* targets; const float* weights; const float* eta;
-  const int32_t *kx, *koff, *cedge, *cj, *pairbase, *blkbase;
-  float *Hpart, *Spart, *vEpart, *Q, *w;
-  int HW, wd, S, tiles_per_split, ntiles, degmax;
-};
 
 __host__ __device__ inline int round4(int x) { return (x + 3) & ~3; }
 
@@ -44,30 +35,6 @@ struct SmemLayout {
   }
 };
 
-// value i of every lane summed onto lane i (tests/test_kernel_algebra.py::test_butterfly_index_map)
-__device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane) {
-#pragma unroll
-  for (int mask = 16, cnt = 32; mask >= 1; mask >>= 1, cnt >>= 1) {
-    const int half = cnt >> 1;
-    const bool up = (lane & mask) != 0;
-#pragma unroll
-    for (int i = 0; i < half; ++i) {
-      float send = up ? v[i] : v[i + half];
-      float keep = up ? v[i + half] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
-    }
-  }
-  return v[0];
-}
-
-__device__ __forceinline__ void decode_pair(int pi, int& A, int& B) {
-  int a = int((sqrtf(8.0f * float(pi) + 1.0f) - 1.0f) * 0.5f);
-  while ((a + 1) * (a + 2) / 2 <= pi) ++a;
-  while (a * (a + 1) / 2 > pi) --a;
-  A = a;
-  B = pi - a * (a + 1) / 2;
-}
-
 template <int PPL, int PPT, bool MOTION_ONLY>
 __global__ void __launch_bounds__(NT, (PPT == 1 ? 2 : 1))
 k_linearize(const LinParams P) {
@@ -82,7 +49,8 @@ k_linearize(const LinParams P) {
   const int BS = L.BS;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int m = blockIdx.x / P.S, s = blockIdx.x % P.S;
+  const int mi = blockIdx.x / P.S, s = blockIdx.x % P.S;
+  const int m = (P.kf_list != nullptr) ? P.kf_list[mi] : mi;
   const int k = P.kx[m];
   const int e0 = P.koff[m];
   const int deg = P.koff[m + 1] - e0;
@@ -127,113 +95,20 @@ k_linearize(const LinParams P) {
       y0[q] = (float(py) - cy) / fy;
     }
     for (int le = warp; le < deg; le += NW) {
-      float Rt[12];
-#pragma unroll
-      for (int i = 0; i < 12; ++i) Rt[i] = sRt[12 * le + i];
       const int e = P.cedge[e0 + le];
-      const float* tg = P.targets + int64_t(e) * 2 * HW;
-      const float* wg = P.weights + int64_t(e) * 2 * HW;
-      float hs[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) hs[i] = 0.f;
-      float* pe = spanel + (1 + le) * BS;
-#pragma unroll
-      for (int q = 0; q < PPL; ++q) {
-        const int pl = lane + 32 * q;
-        const int p = p0 + pl;
-        const bool inb = p < HW;
-        float tx = 0.f, ty = 0.f, wx = 0.f, wy = 0.f;
-        if (inb) {
-          tx = __ldcs(tg + p); ty = __ldcs(tg + HW + p);
-          wx = __ldcs(wg + p); wy = __ldcs(wg + HW + p);
-        }
-        const Proj pr = project(Rt, x0[q], y0[q], d[q], fx, fy, cx, cy);
-        const float r0 = tx - pr.u, r1 = ty - pr.v;
-        const float w0 = kWeightScale * (pr.valid * wx), w1 = kWeightScale * (pr.valid * wy);
-        const float X = pr.X1.x, Y = pr.X1.y, Z = pr.X1.z, dd = d[q];
-        // Jj rows: [d g, X1 x g]
-        float J0[6] = {dd * pr.a0, 0.f, dd * pr.c0, Y * pr.c0, Z * pr.a0 - X * pr.c0, -Y * pr.a0};
-        float J1[6] = {0.f, dd * pr.b1, dd * pr.c1, Y * pr.c1 - Z * pr.b1, -X * pr.c1, X * pr.b1};
-        if (inb) {
-          float wJ0[6], wJ1[6];
-#pragma unroll
-          for (int r = 0; r < 6; ++r) { wJ0[r] = w0 * J0[r]; wJ1[r] = w1 * J1[r]; }
-#pragma unroll
-          for (int r = 0; r < 6; ++r) {
-#pragma unroll
-            for (int c = 0; c <= r; ++c) {
-              if (r != 1 && c != 1) hs[r * (r + 1) / 2 + c] += wJ0[r] * J0[c];
-              if (r != 0 && c != 0) hs[r * (r + 1) / 2 + c] += wJ1[r] * J1[c];
-            }
-            if (r != 1) hs[21 + r] += wJ0[r] * r0;
-            if (r != 0) hs[21 + r] += wJ1[r] * r1;
-          }
-        }
-        if (!MOTION_ONLY) {
-          const float a0 = w0 * pr.jz0, a1 = w1 * pr.jz1;
-          float hx = a0 * pr.a0, hy = a1 * pr.b1, hz = a0 * pr.c0 + a1 * pr.c1;
-          float ck = a0 * pr.jz0 + a1 * pr.jz1;
-          float wk = a0 * r0 + a1 * r1;
-          if (!inb) { hx = hy = hz = ck = wk = 0.f; }
-          pe[0 * T + pl] = hx;                  // rows 0-2 hold h until phase 2 scales them by d
-          pe[1 * T + pl] = hy;
-          pe[2 * T + pl] = hz;
-          pe[3 * T + pl] = Y * hz - Z * hy;     // X1 x h
-          pe[4 * T + pl] = Z * hx - X * hz;
-          pe[5 * T + pl] = X * hy - Y * hx;
-          pe[6 * T + pl] = ck;
-          pe[7 * T + pl] = wk;
-        }
-      }
-      float tot = warp_reduce_scatter32(hs, lane);
-      if (lane < 27) sHacc[le * 32 + lane] += tot;
+      float v[4 * PPL];
+      phase1_load<PPL>(P.targets + int64_t(e) * 2 * HW, P.weights + int64_t(e) * 2 * HW, HW, p0, lane, v);
+      phase1_edge<PPL, MOTION_ONLY>(v, HW, p0, lane, sRt + 12 * le, d, x0, y0, fx, fy, cx, cy,
+                                    spanel + (1 + le) * BS, sHacc + le * 32);
     }
     if (MOTION_ONLY) continue;   // edge `le` always belongs to warp le % NW: no cross-warp hazard
     __syncthreads();
     // ---------------- phase 2: one thread per pixel ---------------------------------------
     if (tid < T) {
-      const int p = p0 + tid;
-      const bool inb = p < HW;
-      const float dd = inb ? __ldg(dk + p) : 0.f;
-      const int py = p / P.wd, px = p - py * P.wd;
-      const float xx = (float(px) - cx) / fx, yy = (float(py) - cy) / fy;
-      float C = 0.f, wsum = 0.f, Gx = 0.f, Gy = 0.f, Gz = 0.f;
-      for (int le = 0; le < deg; ++le) {
-        float* pe = spanel + (1 + le) * BS;
-        const float* R = sRt + 12 * le;
-        float hx = pe[tid], hy = pe[T + tid], hz = pe[2 * T + tid];
-        C += pe[6 * T + tid];
-        wsum += pe[7 * T + tid];
-        Gx += R[0] * hx + R[3] * hy + R[6] * hz;    // R^T h
-        Gy += R[1] * hx + R[4] * hy + R[7] * hz;
-        Gz += R[2] * hx + R[5] * hy + R[8] * hz;
-        pe[tid] = dd * hx; pe[T + tid] = dd * hy; pe[2 * T + tid] = dd * hz;
-      }
-      float Qv = 0.f, wv = 0.f;
-      if (inb) {
-        float et = __ldg(P.eta + int64_t(m) * HW + p);
-        if (P.disps_sens != nullptr) {
-          float ds = __ldg(P.disps_sens + int64_t(k) * HW + p);
-          float ms = ds > 0.f ? 1.f : 0.f;
-          C = C + ms * kSensAlpha + (1.f - ms) * et + kCEps;
-          wsum = wsum - ms * kSensAlpha * (dd - ds);
-        } else {
-          C = C + et + kCEps;
-        }
-        Qv = 1.0f / C;
-        wv = wsum;
-        P.Q[int64_t(m) * HW + p] = Qv;
-        P.w[int64_t(m) * HW + p] = wv;
-      }
+      float Qv, wv;
+      phase2_pixel<T>(P, m, k, deg, p0, tid, dk, sRt, spanel, BS, fx, fy, cx, cy, Qv, wv);
       sq[tid] = Qv;
       sqw[tid] = Qv * wv;
-      // E_ii = -[d G, X0 x G],  X0 = [xx, yy, 1]
-      spanel[0 * T + tid] = -dd * Gx;
-      spanel[1 * T + tid] = -dd * Gy;
-      spanel[2 * T + tid] = -dd * Gz;
-      spanel[3 * T + tid] = -(yy * Gz - Gy);
-      spanel[4 * T + tid] = -(Gx - xx * Gz);
-      spanel[5 * T + tid] = -(xx * Gy - yy * Gx);
     }
     __syncthreads();
     // ---------------- phase 3: Schur products of the panel --------------------------------
@@ -358,16 +233,17 @@ int linearize_pick_ppl(int degmax, int nblkmax, bool motion_only, int HW, size_t
 }
 
 cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, bool motion_only,
-                             int tiles_per_split, int ppl, cudaStream_t st) {
+                             int tiles_per_split, int ppl, const int32_t* kf_list, int nkf, cudaStream_t st) {
   LinParams P;
   P.poses = in.poses; P.disps = in.disps; P.intr = in.intrinsics; P.disps_sens = in.disps_sens;
   P.targets = in.targets; P.weights = in.weights; P.eta = in.eta;
   P.kx = g.kx; P.koff = g.koff; P.cedge = g.cedge; P.cj = g.cj; P.pairbase = g.pairbase; P.blkbase = g.blkbase;
   P.Hpart = ws.Hpart; P.Spart = ws.Spart; P.vEpart = ws.vEpart; P.Q = ws.Q; P.w = ws.w;
+  P.kf_list = kf_list;
   P.HW = g.HW; P.wd = g.wd; P.S = g.S; P.tiles_per_split = tiles_per_split;
   P.ntiles = (g.HW + 31) / 32;   // in units of 32 pixels; the kernel divides by its PPL
   P.degmax = g.degmax;
-  const int grid = g.M * g.S;
+  const int grid = (kf_list != nullptr ? nkf : g.M) * g.S;
   if (grid == 0) return cudaSuccess;
   const size_t smem = linearize_smem_bytes(g.degmax, ppl, motion_only);
   switch (ppl) {

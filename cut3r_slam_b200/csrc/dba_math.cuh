@@ -166,7 +166,9 @@ __device__ __forceinline__ Proj project(const float* Rt, float x0, float y0, flo
   float Z = P.X1.z;
   P.valid = (Z > kMinDepth) ? 1.0f : 0.0f;
   float Zc = (Z < 0.1f) ? 1.0f : Z;
-  float iz = 1.0f / Zc;
+  float iz;                                  // 1/Zc: MUFU.RCP + one Newton step (~0.5 ulp) instead of the IEEE division
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(Zc));
+  iz = iz * fmaf(-Zc, iz, 2.0f);
   P.u = fx * (P.X1.x * iz) + cx;
   P.v = fy * (P.X1.y * iz) + cy;
   P.a0 = fx * iz;
