@@ -21,12 +21,17 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= E) return;
   float hs[27];
+  {  // the split partials are summed in fp64 (a handful of adds; removes one layer of fp32 rounding)
+    double hd[27];
 #pragma unroll
-  for (int i = 0; i < 27; ++i) hs[i] = 0.f;
-  for (int s = 0; s < S; ++s) {
-    const float* src = Hpart + (int64_t(c) * S + s) * 32;
+    for (int i = 0; i < 27; ++i) hd[i] = 0.0;
+    for (int s = 0; s < S; ++s) {
+      const float* src = Hpart + (int64_t(c) * S + s) * 32;
 #pragma unroll
-    for (int i = 0; i < 27; ++i) hs[i] += src[i];
+      for (int i = 0; i < 27; ++i) hd[i] += double(src[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 27; ++i) hs[i] = float(hd[i]);
   }
   float H[36], Ad[36], Rt[12];
 #pragma unroll
@@ -83,7 +88,7 @@ __global__ void __launch_bounds__(36 * ASM_LANES)
 k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ Hblk,
              const float* __restrict__ Spart, int S, int nSblk, float lm, float ep, bool block_diag_quirk,
              float* __restrict__ A, int ldA) {
-  __shared__ float sh[ASM_LANES][36], ss[ASM_LANES][36];
+  __shared__ double sh[ASM_LANES][36], ss[ASM_LANES][36];
   const int ob = blockIdx.x;
   const int il = threadIdx.x / 36, ent = threadIdx.x % 36;
   const int r = ent / 6, c = ent % 6;
@@ -92,19 +97,21 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
   while ((a + 1) * (a + 2) / 2 <= ob) ++a;
   while (a * (a + 1) / 2 > ob) --a;
   const int b = ob - a * (a + 1) / 2;
-  float hsum = 0.f, ssum = 0.f;
+  // gathers are summed in fp64: S = H - E Q E^T cancels several digits, so the only roundings kept
+  // are those of the fp32 partials themselves and the final store
+  double hsum = 0.0, ssum = 0.0;
   const int i0 = off[ob], i1 = off[ob + 1];
   for (int i = i0 + il; i < i1; i += ASM_LANES) {
     const Item it = items[i];
     const int e = (it.flags & 2) ? (c * 6 + r) : ent;
     if ((it.flags & 1) == 0) {
-      hsum += __ldcg(Hblk + int64_t(it.base) * 36 + e);
+      hsum += double(__ldcg(Hblk + int64_t(it.base) * 36 + e));
     } else {
       const float* src = Spart + int64_t(it.base) * 36 + e;
       const int64_t st = int64_t(it.stride) * 36;
-      float t = 0.f;
+      double t = 0.0;
 #pragma unroll 4
-      for (int s = 0; s < S; ++s) t += __ldcg(src + s * st);
+      for (int s = 0; s < S; ++s) t += double(__ldcg(src + s * st));
       ssum += t;
     }
   }
@@ -117,9 +124,9 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
   // chol.py:55-57: H + (ep + lm H) on the true diagonal; chol.py:35-37 (block_solve as written):
   // on the diagonal of EVERY 6x6 block when the quirk is requested (motion_only parity switch)
   const bool damp = (r == c) && (a == b || block_diag_quirk);
-  float val = damp ? hsum + (ep + lm * hsum) : hsum;
+  double val = damp ? hsum + (double(ep) + double(lm) * hsum) : hsum;
   val -= ssum;
-  A[int64_t(6 * a + r) * ldA + 6 * b + c] = val;
+  A[int64_t(6 * a + r) * ldA + 6 * b + c] = float(val);
 }
 
 // rhs row of the augmented system: v - E Q w.  One CTA per pose: 16 item lanes x 6 entries.
@@ -128,20 +135,20 @@ constexpr int RHS_LANES = 16;
 __global__ void __launch_bounds__(6 * RHS_LANES)
 k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ vblk,
                const float* __restrict__ vEpart, int S, int Pp, float* __restrict__ A, int ldA) {
-  __shared__ float sv[RHS_LANES][6], se[RHS_LANES][6];
+  __shared__ double sv[RHS_LANES][6], se[RHS_LANES][6];
   const int a = blockIdx.x;
   const int il = threadIdx.x / 6, r = threadIdx.x % 6;
-  float vsum = 0.f, esum = 0.f;
+  double vsum = 0.0, esum = 0.0;
   for (int i = off[a] + il; i < off[a + 1]; i += RHS_LANES) {
     const Item it = items[i];
     if ((it.flags & 1) == 0) {
-      vsum += __ldcg(vblk + int64_t(it.base) * 6 + r);
+      vsum += double(__ldcg(vblk + int64_t(it.base) * 6 + r));
     } else {
       const float* src = vEpart + int64_t(it.base) * 6 + r;
       const int64_t st = int64_t(it.stride) * 6;
-      float t = 0.f;
+      double t = 0.0;
 #pragma unroll 4
-      for (int s = 0; s < S; ++s) t += __ldcg(src + s * st);
+      for (int s = 0; s < S; ++s) t += double(__ldcg(src + s * st));
       esum += t;
     }
   }
@@ -151,7 +158,7 @@ k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, 
   if (il != 0) return;
 #pragma unroll
   for (int l = 1; l < RHS_LANES; ++l) { vsum += sv[l][r]; esum += se[l][r]; }
-  A[int64_t(6 * Pp) * ldA + a * 6 + r] = vsum - esum;
+  A[int64_t(6 * Pp) * ldA + a * 6 + r] = float(vsum - esum);
 }
 
 // ---------------------------------------------------------------------------------------------
