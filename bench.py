@@ -150,6 +150,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="libdba option name=value (developer experiments)")
+    ap.add_argument("--brief", action="store_true", help="print only ms/step and the per-stage times")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -172,6 +174,9 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
+    for o in args.opt:
+        k_, v_ = o.split("=")
+        db.set_option(k_, float(v_), dev)
     cfg = CONFIGS[args.workload]
     p = make_problem(args.workload)
     E, HW, Pp = p.ii.numel(), p.disps.shape[1] * p.disps.shape[2], p.t1 - p.t0
@@ -273,7 +278,10 @@ def main():
     b_alg = algorithmic_bytes(E, HW, M, Pp, p.motion_only)
     whole = b_alg * iters / (ms_step * 1e-3) / 1e9
 
-    if rank == 0:
+    if rank == 0 and args.brief:
+        print(json.dumps({"opts": args.opt, "ms_per_step": round(ms_step, 4), "ms_e2e": round(ms_e2e, 4),
+                          "stage_us": {k: round(v * 1e3, 1) for k, v in stage_ms.items()}}), flush=True)
+    elif rank == 0:
         ep_per_s = E * HW * iters / (ms_step * 1e-3)
         line = {
             "metric": "ba_edge_pixels_per_s", "value": ep_per_s, "unit": "edge-pixels/s", "n_gpus": world,

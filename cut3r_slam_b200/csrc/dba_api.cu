@@ -85,6 +85,8 @@ struct dba_ctx {
   bool profile = false;            // CUDA events around every stage (adds a sync at the end of the call)
   double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // linearize, assemble, allreduce, cholesky, backsub, retract, -, launches
   std::vector<cudaEvent_t> ev;
+  cudaStream_t side = nullptr;       // the few high-degree keyframes (SIMT kernel) run beside the tcgen05 launch
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int opt_splits = 0;
   int opt_ppl = 0;
   // plan cache
@@ -318,9 +320,18 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   for (int it = 0; it < iterations; ++it) {
     mark();
     if (g.E > 0) {
+      const bool fork = g.n_tc > 0 && g.n_simt > 0 && ctx->side != nullptr;
+      if (fork) {   // long SIMT CTAs first (side stream) so that they do not form the tail of the stage
+        CK(cudaEventRecord(ctx->ev_fork, st), "fork");
+        CK(cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0), "fork");
+        CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, ctx->side), "linearize");
+        CK(cudaEventRecord(ctx->ev_join, ctx->side), "join");
+      }
       if (g.n_tc > 0)
         CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, st), "linearize (tcgen05)");
-      if (g.n_simt > 0)
+      if (fork)
+        CK(cudaStreamWaitEvent(st, ctx->ev_join, 0), "join");
+      else if (g.n_simt > 0)
         CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, st), "linearize");
     }
     mark();
@@ -394,6 +405,14 @@ dba_ctx* dba_create(int device) {
   int cap = 0;
   cudaDeviceGetAttribute(&cap, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
   c->smem_cap = size_t(cap);
+  int lo_pri = 0, hi_pri = 0;
+  cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri);
+  if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, hi_pri) != cudaSuccess) c->side = nullptr;
+  if (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    if (c->side) cudaStreamDestroy(c->side);
+    c->side = nullptr;
+  }
   return c;
 }
 
@@ -406,6 +425,9 @@ void dba_destroy(dba_ctx* c) {
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+  if (c->side) cudaStreamDestroy(c->side);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->h_idx) cudaFreeHost(c->h_idx);
   delete c;
 }
@@ -420,6 +442,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
   else if (n == "tensor_cores") { ctx->opt_tc = value != 0; ctx->plan_valid = false; }
+  else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {
     int v = int(value);

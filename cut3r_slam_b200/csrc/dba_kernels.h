@@ -59,6 +59,7 @@ cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Wor
 cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
                                 const int32_t* kf_list, int nkf, int degmax, cudaStream_t st);
 size_t linearize_tc_smem_bytes(int degmax);
+extern int g_tc_stream_mode;
 int linearize_tc_max_degree();
 int linearize_tc_ppl();
 size_t linearize_smem_bytes(int degmax, int ppl, bool motion_only);
