@@ -39,6 +39,12 @@ SIGNATURES = {
     "dba_plan_build": (C.c_void_p, [c_i, c_i, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
                                     C.c_char_p, C.c_int]),
     "dba_plan_free": (None, [C.c_void_p]),
+    "dba_graph_neighbourhood": (C.c_int64, [C.c_int64, C.c_int64, C.c_int64, c_i, c_i, C.c_int64]),
+    "dba_graph_filter_repeated": (C.c_int64, [c_i, c_i, C.c_int64, c_i, c_i, C.c_int64, C.c_void_p]),
+    "dba_graph_evict_mask": (C.c_int64, [c_i, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "dba_graph_rm_keyframe": (C.c_int64, [c_i, c_i, c_i, C.c_int64, C.c_int64]),
+    "dba_graph_proximity": (C.c_int64, [c_f, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_float,
+                                        C.c_int64, c_i, c_i, C.c_int64, c_i, c_i, C.c_int64]),
     "dba_plan_get": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64]),
 }
 

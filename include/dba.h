@@ -102,6 +102,23 @@ void* dba_plan_build(const int64_t* ii, const int64_t* jj, int64_t E, int N, int
 void dba_plan_free(void* plan);
 int64_t dba_plan_get(void* plan, const char* name, int32_t* out, int64_t cap);
 
+/* ---- edge bookkeeping on HOST int64 arrays (bit-exact restatement of hislam2/geom/graph_utils.py:20-29 and
+ * hislam2/factor_graph.py:29-39,59-117; proximity selection from factor_graph.pyc add_proximity_factors@354-424).
+ * Order of appended edges is the reference's.  No GPU involved. */
+/* (i,j) in [t0,t1)^2, row-major, 1 <= |i-j| <= r (neighbourhood_graph / add_neighborhood_factors); returns count */
+int64_t dba_graph_neighbourhood(int64_t t0, int64_t t1, int64_t r, int64_t* ii, int64_t* jj, int64_t cap);
+/* keep[k] = new edge k is not in the current graph (__filter_repeated_edges); returns number kept */
+int64_t dba_graph_filter_repeated(const int64_t* cur_ii, const int64_t* cur_jj, int64_t n_cur, const int64_t* new_ii,
+                                  const int64_t* new_jj, int64_t n_new, uint8_t* keep);
+/* add_factors' eviction mask when max_factors would be exceeded (factor_graph.py:75-77); returns number removed */
+int64_t dba_graph_evict_mask(const int64_t* age, int64_t n, int64_t max_factors, int64_t n_new, uint8_t* remove);
+/* rm_keyframe on the edge lists (factor_graph.py:100-106), in place; age may be NULL; returns the new count */
+int64_t dba_graph_rm_keyframe(int64_t* ii, int64_t* jj, int64_t* age, int64_t n, int64_t ix);
+/* add_proximity_factors' edge selection; d [(t-t0)*(t-t1)] from frame_distance is modified in place */
+int64_t dba_graph_proximity(float* d, int64_t t0, int64_t t1, int64_t t, int64_t rad, int64_t nms, float thresh,
+                            int64_t max_factors, const int64_t* ex_ii, const int64_t* ex_jj, int64_t n_ex,
+                            int64_t* out_ii, int64_t* out_jj, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif
