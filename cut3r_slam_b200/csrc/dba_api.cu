@@ -237,6 +237,12 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   size_t o_kx = put(P.kx), o_koff = put(P.koff), o_cedge = put(P.cedge), o_ci = put(P.ci), o_cj = put(P.cj);
   size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
   size_t o_tc = put(tc_list), o_sl = put(simt_list);
+  std::vector<int32_t> blist, heavy;
+  for (int ob = 0; ob < P.nSblk; ++ob)
+    (P.sblk_off[ob + 1] - P.sblk_off[ob] <= 8 ? blist : heavy).push_back(ob);
+  const int n_light = int(blist.size());
+  blist.insert(blist.end(), heavy.begin(), heavy.end());
+  size_t o_bl = put(blist);
   CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
   CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
   std::vector<Item> items(P.sblk_items);
@@ -261,6 +267,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   g.sblk_items = ctx->d_items.as<Item>();
   g.rhs_items = ctx->d_items.as<Item>() + n_s;
   g.nSblk = P.nSblk;
+  g.sblk_list = base + o_bl; g.n_light = n_light;
   ctx->plan_valid = true;
   return 0;
 }

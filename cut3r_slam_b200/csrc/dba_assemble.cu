@@ -15,65 +15,71 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // per edge: sum the split partials of Hjj / vj, expand to the four 6x6 blocks with the adjoint
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+constexpr int EF_WARPS = 8;
+
+// one warp per edge: lanes 0..26 sum the split partials (fp64: a handful of adds, removes one layer of
+// fp32 rounding), the 4 x 36 + 2 x 6 outputs are spread over the lanes
+__global__ void __launch_bounds__(32 * EF_WARPS)
 k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci, const int32_t* __restrict__ cj,
                 const float* __restrict__ Hpart, int E, int S, float* __restrict__ Hblk, float* __restrict__ vblk) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float sH[EF_WARPS][36], sHij[EF_WARPS][36], sAd[EF_WARPS][36], sv[EF_WARPS][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * EF_WARPS + warp;
   if (c >= E) return;
-  float hs[27];
-  {  // the split partials are summed in fp64 (a handful of adds; removes one layer of fp32 rounding)
-    double hd[27];
-#pragma unroll
-    for (int i = 0; i < 27; ++i) hd[i] = 0.0;
-    for (int s = 0; s < S; ++s) {
-      const float* src = Hpart + (int64_t(c) * S + s) * 32;
-#pragma unroll
-      for (int i = 0; i < 27; ++i) hd[i] += double(src[i]);
+  {
+    double hd = 0.0;
+    const float* src = Hpart + int64_t(c) * S * 32 + lane;
+    for (int s = 0; s < S; ++s) hd += double(__ldcg(src + s * 32));
+    const float hv = float(hd);
+    // lane l < 21 holds H[r][cc] with l = r(r+1)/2 + cc (cc <= r); lanes 21..26 hold vj
+    if (lane < 21) {
+      int r = 0;
+      while ((r + 1) * (r + 2) / 2 <= lane) ++r;
+      const int cc = lane - r * (r + 1) / 2;
+      sH[warp][r * 6 + cc] = hv;
+      sH[warp][cc * 6 + r] = hv;
+    } else if (lane < 27) {
+      sv[warp][lane - 21] = hv;
     }
-#pragma unroll
-    for (int i = 0; i < 27; ++i) hs[i] = float(hd[i]);
   }
-  float H[36], Ad[36], Rt[12];
+  if (lane == 31) {      // an otherwise idle lane builds the adjoint of the edge's relative pose
+    float AdR[36], Rt[12];
+    relative_pose_Rt(poses, ci[c], cj[c], Rt);
+    adjoint_from_Rt(Rt, AdR);
 #pragma unroll
-  for (int r = 0; r < 6; ++r)
-#pragma unroll
-    for (int cc = 0; cc <= r; ++cc) { H[r * 6 + cc] = hs[r * (r + 1) / 2 + cc]; H[cc * 6 + r] = H[r * 6 + cc]; }
-  relative_pose_Rt(poses, ci[c], cj[c], Rt);
-  adjoint_from_Rt(Rt, Ad);
+    for (int i = 0; i < 36; ++i) sAd[warp][i] = AdR[i];
+  }
+  __syncwarp();
+  const float* H = sH[warp];
+  const float* Ad = sAd[warp];
   float* out = Hblk + int64_t(c) * 144;
-  float Hij[36];   // -Ad^T Hjj
+  for (int e = lane; e < 36; e += 32) {          // Hij = -Ad^T Hjj ; Hji = -Hjj Ad ; Hjj
+    const int r = e / 6, cc = e - r * 6;
+    float a = 0.f, hji = 0.f;
 #pragma unroll
-  for (int r = 0; r < 6; ++r)
-#pragma unroll
-    for (int cc = 0; cc < 6; ++cc) {
-      float a = 0.f;
-#pragma unroll
-      for (int t = 0; t < 6; ++t) a += Ad[t * 6 + r] * H[t * 6 + cc];
-      Hij[r * 6 + cc] = -a;
+    for (int t = 0; t < 6; ++t) {
+      a += Ad[t * 6 + r] * H[t * 6 + cc];
+      hji += H[r * 6 + t] * Ad[t * 6 + cc];
     }
+    sHij[warp][e] = -a;
+    out[1 * 36 + e] = -a;
+    out[2 * 36 + e] = -hji;
+    out[3 * 36 + e] = H[e];
+  }
+  __syncwarp();
+  for (int e = lane; e < 36; e += 32) {          // Hii = Ad^T Hjj Ad = -(Hij Ad)
+    const int r = e / 6, cc = e - r * 6;
+    float hii = 0.f;
 #pragma unroll
-  for (int r = 0; r < 6; ++r)
-#pragma unroll
-    for (int cc = 0; cc < 6; ++cc) {
-      float hii = 0.f, hji = 0.f;
-#pragma unroll
-      for (int t = 0; t < 6; ++t) {
-        hii += Hij[r * 6 + t] * Ad[t * 6 + cc];     // (-Ad^T H)(Ad) -> negate below
-        hji += H[r * 6 + t] * Ad[t * 6 + cc];
-      }
-      out[0 * 36 + r * 6 + cc] = -hii;              // Hii = Ad^T Hjj Ad
-      out[1 * 36 + r * 6 + cc] = Hij[r * 6 + cc];   // Hij
-      out[2 * 36 + r * 6 + cc] = -hji;              // Hji = -Hjj Ad
-      out[3 * 36 + r * 6 + cc] = H[r * 6 + cc];     // Hjj
-    }
-  float* vo = vblk + int64_t(c) * 12;
-#pragma unroll
-  for (int r = 0; r < 6; ++r) {
+    for (int t = 0; t < 6; ++t) hii += sHij[warp][r * 6 + t] * Ad[t * 6 + cc];
+    out[e] = -hii;
+  }
+  if (lane < 6) {
     float a = 0.f;
 #pragma unroll
-    for (int t = 0; t < 6; ++t) a += Ad[t * 6 + r] * hs[21 + t];
-    vo[r] = -a;                 // vi = -Ad^T vj
-    vo[6 + r] = hs[21 + r];     // vj
+    for (int t = 0; t < 6; ++t) a += Ad[t * 6 + lane] * sv[warp][t];
+    vblk[int64_t(c) * 12 + lane] = -a;                   // vi = -Ad^T vj
+    vblk[int64_t(c) * 12 + 6 + lane] = sv[warp][lane];   // vj
   }
 }
 
@@ -84,26 +90,14 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
 // ---------------------------------------------------------------------------------------------
 constexpr int ASM_LANES = 8;
 
-__global__ void __launch_bounds__(36 * ASM_LANES)
-k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ Hblk,
-             const float* __restrict__ Spart, int S, int nSblk, float lm, float ep, bool block_diag_quirk,
-             float* __restrict__ A, int ldA) {
-  __shared__ double sh[ASM_LANES][36], ss[ASM_LANES][36];
-  const int ob = blockIdx.x;
-  const int il = threadIdx.x / 36, ent = threadIdx.x % 36;
-  const int r = ent / 6, c = ent % 6;
-  // ob = a(a+1)/2 + b
-  int a = int((sqrtf(8.0f * float(ob) + 1.0f) - 1.0f) * 0.5f);
-  while ((a + 1) * (a + 2) / 2 <= ob) ++a;
-  while (a * (a + 1) / 2 > ob) --a;
-  const int b = ob - a * (a + 1) / 2;
-  // gathers are summed in fp64: S = H - E Q E^T cancels several digits, so the only roundings kept
-  // are those of the fp32 partials themselves and the final store
-  double hsum = 0.0, ssum = 0.0;
-  const int i0 = off[ob], i1 = off[ob + 1];
-  for (int i = i0 + il; i < i1; i += ASM_LANES) {
+// gathers of one 6x6 block entry: items i0+il, i0+il+nl, ... (fp64 sums: S = H - E Q E^T cancels several
+// digits, so the only roundings kept are those of the fp32 partials themselves and the final store)
+__device__ __forceinline__ void gather_block(const Item* __restrict__ items, int i0, int i1, int il, int nl, int ent,
+                                             int entT, const float* __restrict__ Hblk,
+                                             const float* __restrict__ Spart, int S, double& hsum, double& ssum) {
+  for (int i = i0 + il; i < i1; i += nl) {
     const Item it = items[i];
-    const int e = (it.flags & 2) ? (c * 6 + r) : ent;
+    const int e = (it.flags & 2) ? entT : ent;
     if ((it.flags & 1) == 0) {
       hsum += double(__ldcg(Hblk + int64_t(it.base) * 36 + e));
     } else {
@@ -115,12 +109,44 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
       ssum += t;
     }
   }
-  sh[il][ent] = hsum;
-  ss[il][ent] = ssum;
-  __syncthreads();
-  if (il != 0) return;
+}
+
+// CTAs [0, nlightCTA): 8 light blocks (<= 8 items) per CTA, one thread per entry; the remaining CTAs: one
+// heavy block (diagonal blocks carry ~50 items) with 8 item lanes per entry, summed in lane order.
+__global__ void __launch_bounds__(36 * ASM_LANES)
+k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const int32_t* __restrict__ blist,
+             int nlight, int nlightCTA, const float* __restrict__ Hblk, const float* __restrict__ Spart, int S,
+             float lm, float ep, bool block_diag_quirk, float* __restrict__ A, int ldA) {
+  __shared__ double sh[ASM_LANES][36], ss[ASM_LANES][36];
+  const bool light = int(blockIdx.x) < nlightCTA;
+  const int grp = threadIdx.x / 36, ent = threadIdx.x % 36;
+  const int r = ent / 6, c = ent % 6;
+  int ob;
+  if (light) {
+    const int idx = blockIdx.x * ASM_LANES + grp;
+    if (idx >= nlight) return;
+    ob = blist[idx];
+  } else {
+    ob = blist[nlight + (blockIdx.x - nlightCTA)];
+  }
+  // ob = a(a+1)/2 + b
+  int a = int((sqrtf(8.0f * float(ob) + 1.0f) - 1.0f) * 0.5f);
+  while ((a + 1) * (a + 2) / 2 <= ob) ++a;
+  while (a * (a + 1) / 2 > ob) --a;
+  const int b = ob - a * (a + 1) / 2;
+  double hsum = 0.0, ssum = 0.0;
+  const int i0 = off[ob], i1 = off[ob + 1];
+  if (light) {
+    gather_block(items, i0, i1, 0, 1, ent, c * 6 + r, Hblk, Spart, S, hsum, ssum);
+  } else {
+    gather_block(items, i0, i1, grp, ASM_LANES, ent, c * 6 + r, Hblk, Spart, S, hsum, ssum);
+    sh[grp][ent] = hsum;
+    ss[grp][ent] = ssum;
+    __syncthreads();
+    if (grp != 0) return;
 #pragma unroll
-  for (int l = 1; l < ASM_LANES; ++l) { hsum += sh[l][ent]; ssum += ss[l][ent]; }
+    for (int l = 1; l < ASM_LANES; ++l) { hsum += sh[l][ent]; ssum += ss[l][ent]; }
+  }
   // chol.py:55-57: H + (ep + lm H) on the true diagonal; chol.py:35-37 (block_solve as written):
   // on the diagonal of EVERY 6x6 block when the quirk is requested (motion_only parity switch)
   const bool damp = (r == c) && (a == b || block_diag_quirk);
@@ -271,11 +297,13 @@ cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Work
                             float /*hscale_lm*/, bool motion_only, bool block_diag_quirk, cudaStream_t st) {
   (void)motion_only;
   if (g.E > 0) {
-    k_edge_finalize<<<(g.E + 127) / 128, 128, 0, st>>>(in.poses, g.ci, g.cj, ws.Hpart, g.E, g.S, ws.Hblk, ws.vblk);
+    k_edge_finalize<<<(g.E + EF_WARPS - 1) / EF_WARPS, 32 * EF_WARPS, 0, st>>>(in.poses, g.ci, g.cj, ws.Hpart, g.E, g.S, ws.Hblk, ws.vblk);
     g_launch_count++;
   }
-  k_assemble_S<<<g.nSblk, 36 * ASM_LANES, 0, st>>>(
-      g.sblk_off, g.sblk_items, ws.Hblk, ws.Spart, g.S, g.nSblk, lm, ep, block_diag_quirk, ws.A, ws.ldA);
+  const int nlightCTA = (g.n_light + ASM_LANES - 1) / ASM_LANES;
+  k_assemble_S<<<nlightCTA + (g.nSblk - g.n_light), 36 * ASM_LANES, 0, st>>>(
+      g.sblk_off, g.sblk_items, g.sblk_list, g.n_light, nlightCTA, ws.Hblk, ws.Spart, g.S, lm, ep, block_diag_quirk,
+      ws.A, ws.ldA);
   k_assemble_rhs<<<g.Pp, 6 * RHS_LANES, 0, st>>>(g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.S, g.Pp,
                                                          ws.A, ws.ldA);
   g_launch_count += 2;

@@ -439,6 +439,82 @@ k_backsolve(const float* __restrict__ Lm, const float* __restrict__ Ldiag, int l
   if (tid == 0) { *fail = 0; *bar = 0u; }
 }
 
+
+// ---- backward solve, shared-memory variant (n <= ~830): the 32-row slab of L that step k multiplies
+// with x_k does not depend on x, so the slab of step k-1 streams into the other half of a double
+// buffer (cp.async) while step k computes: no L2 latency on the chain.
+constexpr int BSW_MAX = 832;             // widest slab (columns) that fits twice in shared memory
+
+__host__ __device__ inline size_t backsolve_smem_floats(int n, int W) {
+  return size_t(2 * NB * NB) + size_t(n + NB) + size_t(2) * NB * W;
+}
+
+__global__ void __launch_bounds__(BSN)
+k_backsolve_smem(const float* __restrict__ Lm, const float* __restrict__ Ldiag, int ld, int n, int W, int* fail,
+                 unsigned* bar, float* __restrict__ dx) {
+  extern __shared__ __align__(16) float bsm[];
+  float* sLi = bsm;                      // [2][32][32]
+  float* slab = bsm + 2 * NB * NB;       // [2][32][W]
+  float* xs = slab + 2 * NB * W;         // [n + 32]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nkb = (n + NB - 1) / NB;
+  auto prefetch = [&](int kb) {          // slab rows k0..k0+31 (columns < k0) and L_kk^-1 of block kb
+    const int k0 = kb * NB, nb = min(NB, n - k0);
+    float* dst = slab + (kb & 1) * NB * W;
+    const int cpr = k0 >> 2;             // 16-byte chunks per row
+    for (int i = tid; i < NB * cpr; i += BSN) {
+      const int r = i / cpr, ch = i - r * cpr;
+      cp_async16(dst + r * W + ch * 4, Lm + int64_t(k0 + r) * ld + ch * 4, r < nb);
+    }
+    if (tid < NB * NB / 4)
+      cp_async16(sLi + (kb & 1) * NB * NB + tid * 4, Ldiag + int64_t(kb) * LD_STRIDE + LD_LINV + tid * 4, true);
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+  prefetch(nkb - 1);
+  for (int i = tid; i < n + NB; i += BSN) xs[i] = (i < n) ? __ldcg(Lm + int64_t(n) * ld + i) : 0.f;
+  for (int kb = nkb - 1; kb >= 0; --kb) {
+    const int k0 = kb * NB, nb = min(NB, n - k0);
+    if (kb > 0) {
+      prefetch(kb - 1);
+      asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    }
+    __syncthreads();                     // slab / L_kk^-1 of step kb landed; xs of the previous step complete
+    if (warp == 0) {
+      const float* Li = sLi + (kb & 1) * NB * NB;
+      float x = 0.f;
+#pragma unroll
+      for (int r = 0; r < NB; ++r) x = fmaf(Li[r * NB + lane], xs[k0 + r], x);
+      __syncwarp();
+      if (lane < nb) xs[k0 + lane] = x;
+    }
+    __syncthreads();
+    const float* sl = slab + (kb & 1) * NB * W;
+    float xk[NB];
+#pragma unroll
+    for (int r4 = 0; r4 < NB; r4 += 4) {
+      const float4 v = *reinterpret_cast<const float4*>(xs + k0 + r4);
+      xk[r4] = v.x; xk[r4 + 1] = v.y; xk[r4 + 2] = v.z; xk[r4 + 3] = v.w;
+    }
+    for (int c = tid; c < k0; c += BSN) {
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int r = 0; r < NB; r += 2) {
+        s0 = fmaf(sl[r * W + c], xk[r], s0);
+        s1 = fmaf(sl[(r + 1) * W + c], xk[r + 1], s1);
+      }
+      xs[c] -= s0 + s1;
+    }
+    __syncthreads();                     // slab (kb & 1) is free for the prefetch of step kb - 2
+  }
+  __syncthreads();
+  const int failed = *reinterpret_cast<volatile int*>(fail);
+  __syncthreads();
+  for (int i = tid; i < n; i += BSN) dx[i] = failed ? 0.f : xs[i];
+  if (tid == 0) { *fail = 0; *bar = 0u; }
+}
+
 }  // namespace
 
 #ifdef DBA_CHOL_TRACE
@@ -458,8 +534,17 @@ cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaS
   cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_chol_fused), dim3(grid), dim3(NTH), args, 0, st);
   g_launch_count++;
   if (err != cudaSuccess) return err;
-  const size_t smem = size_t(2 * NB * NB + n + NB) * sizeof(float);
-  k_backsolve<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, fail, bar, dx);
+  const int nkb = (n + NB - 1) / NB;
+  const int W = (nkb - 1) * NB > 0 ? (nkb - 1) * NB : 4;
+  if (W <= BSW_MAX) {
+    const size_t smem = backsolve_smem_floats(n, W) * sizeof(float);
+    err = cudaFuncSetAttribute(k_backsolve_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (err != cudaSuccess) return err;
+    k_backsolve_smem<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, W, fail, bar, dx);
+  } else {
+    const size_t smem = size_t(2 * NB * NB + n + NB) * sizeof(float);
+    k_backsolve<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, fail, bar, dx);
+  }
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -23,6 +23,9 @@ struct DeviceGraph {
   const int32_t *sblk_off, *rhs_off;
   const Item *sblk_items, *rhs_items;
   int nSblk;
+  // blocks of S by gather-list length: [0, n_light) have <= 8 items (8 blocks per CTA), the rest one CTA each
+  const int32_t* sblk_list;
+  int n_light;
 };
 
 struct BAInputs {
