@@ -264,6 +264,13 @@ def main():
     stages, n_it = db.stage_times(dev)
     db.set_option("profile", 0, dev)
     stage_ms = {k: v / max(n_it, 1) for k, v in stages.items()}          # per LM iteration
+    stage_all = None
+    if world > 1:                                                         # every rank's stage times (diagnosis of skew)
+        keys = sorted(stage_ms)
+        mine_t = torch.tensor([stage_ms[k] for k in keys], dtype=torch.float64, device=dev)
+        allt = [torch.zeros_like(mine_t) for _ in range(world)]
+        dist.all_gather(allt, mine_t)
+        stage_all = {k: [round(float(t[i]) * 1e3, 1) for t in allt] for i, k in enumerate(keys)}
     E_loc = int(sel.numel())
     lin_bytes = linearize_bytes(E_loc, HW, hi - lo)
     peaks = {}
@@ -280,7 +287,8 @@ def main():
 
     if rank == 0 and args.brief:
         print(json.dumps({"opts": args.opt, "ms_per_step": round(ms_step, 4), "ms_e2e": round(ms_e2e, 4),
-                          "stage_us": {k: round(v * 1e3, 1) for k, v in stage_ms.items()}}), flush=True)
+                          "stage_us": {k: round(v * 1e3, 1) for k, v in stage_ms.items()},
+                          "stage_us_per_rank": stage_all}), flush=True)
     elif rank == 0:
         ep_per_s = E * HW * iters / (ms_step * 1e-3)
         line = {
@@ -303,6 +311,7 @@ def main():
                          "whole_iteration": {"algorithmic_bytes": b_alg, "achieved": whole, "frac": whole / peak,
                                              "frac_of_8TBs_nominal": whole / 8000.0}},
             "stage_ms_per_lm_iteration": stage_ms,
+            "stage_us_per_rank": stage_all,
         }
         if not args.no_cpu_baseline and world == 1:
             import oracle.dba as od

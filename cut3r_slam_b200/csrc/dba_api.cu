@@ -177,19 +177,39 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
     if (use_tc) {
       // CTAs are dispatched in block order onto 2 slots per SM: simulate that list schedule for every
       // split count (jobs = keyframes sorted by out-degree x pixel splits) and keep the shortest
-      std::vector<int> dg(N, 0), degs;
+      std::vector<int> dg(N, 0), degs, wide;
       for (int64_t e = 0; e < E; ++e) dg[ii[e]]++;
-      for (int f = 0; f < N; ++f)
+      for (int f = 0; f < N; ++f) {
         if (dg[f] > 0 && dg[f] <= linearize_tc_max_degree()) degs.push_back(dg[f]);
+        else if (dg[f] > 0) wide.push_back(dg[f]);
+      }
       std::sort(degs.begin(), degs.end(), std::greater<int>());
+      std::sort(wide.begin(), wide.end(), std::greater<int>());
       const int slots = 2 * sm;
       double best = 1e300;
-      for (int cand = 1; cand <= 16 && cand <= ntilesT; ++cand) {
+      // measured (backend graph, 1 GPU): flat optimum for 2..5 waves of CTAs, clearly slower below; so only
+      // split counts that give >= 2.5 waves compete (capped at 2 tiles per CTA), the simulation picks among them
+      const int njobs = int(degs.size() + 2 * wide.size());
+      int cand_lo = 1;
+      while (cand_lo < ntilesT && (ntilesT + cand_lo - 1) / cand_lo > 2 && njobs * cand_lo < (5 * slots) / 2) ++cand_lo;
+      for (int cand = cand_lo; cand <= 52 && cand <= ntilesT; ++cand) {
         const int tps_c = (ntilesT + cand - 1) / cand, S_c = (ntilesT + tps_c - 1) / tps_c;
-        if (S_c != cand) continue;
+        if (S_c != cand && cand != cand_lo) continue;
+        if (S_c != cand) { continue; }
         std::priority_queue<double, std::vector<double>, std::greater<double>> free_at;
         for (int i = 0; i < slots; ++i) free_at.push(0.0);
         double makespan = 0.0;
+        // the SIMT CTAs of the wide keyframes start first (side stream) and take a whole SM = two slots;
+        // measured: a 64-pixel tile costs ~0.064 (deg+1)^2 of the unit in which a tcgen05 tile costs deg + 6
+        for (int dgk : wide)
+          for (int sp = 0; sp < S_c; ++sp) {
+            const int nt = std::min(tps_c, ntilesT - sp * tps_c);
+            const double a = free_at.top(); free_at.pop();
+            const double b = free_at.top(); free_at.pop();
+            const double t1s = std::max(a, b) + 4.0 + nt * 0.064 * (dgk + 1.0) * (dgk + 1.0);
+            free_at.push(t1s); free_at.push(t1s);
+            if (t1s > makespan) makespan = t1s;
+          }
         for (int dgk : degs)
           for (int sp = 0; sp < S_c; ++sp) {
             const int nt = std::min(tps_c, ntilesT - sp * tps_c);
@@ -238,8 +258,10 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
   size_t o_tc = put(tc_list), o_sl = put(simt_list);
   std::vector<int32_t> blist, heavy;
+  // small systems: every block gets its own CTA (8 item lanes); large ones: blocks with <= 8 items share a CTA
+  const bool all_heavy = P.nSblk <= 1184;
   for (int ob = 0; ob < P.nSblk; ++ob)
-    (P.sblk_off[ob + 1] - P.sblk_off[ob] <= 8 ? blist : heavy).push_back(ob);
+    (!all_heavy && P.sblk_off[ob + 1] - P.sblk_off[ob] <= 8 ? blist : heavy).push_back(ob);
   const int n_light = int(blist.size());
   blist.insert(blist.end(), heavy.begin(), heavy.end());
   size_t o_bl = put(blist);

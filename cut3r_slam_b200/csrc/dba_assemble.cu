@@ -16,6 +16,7 @@ namespace {
 // per edge: sum the split partials of Hjj / vj, expand to the four 6x6 blocks with the adjoint
 // ---------------------------------------------------------------------------------------------
 constexpr int EF_WARPS = 8;
+__device__ __forceinline__ double sum_splits(const float* __restrict__ src, int64_t st, int S);
 
 // one warp per edge: lanes 0..26 sum the split partials (fp64: a handful of adds, removes one layer of
 // fp32 rounding), the 4 x 36 + 2 x 6 outputs are spread over the lanes
@@ -27,10 +28,7 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
   const int c = blockIdx.x * EF_WARPS + warp;
   if (c >= E) return;
   {
-    double hd = 0.0;
-    const float* src = Hpart + int64_t(c) * S * 32 + lane;
-    for (int s = 0; s < S; ++s) hd += double(__ldcg(src + s * 32));
-    const float hv = float(hd);
+    const float hv = float(sum_splits(Hpart + int64_t(c) * S * 32 + lane, 32, S));
     // lane l < 21 holds H[r][cc] with l = r(r+1)/2 + cc (cc <= r); lanes 21..26 hold vj
     if (lane < 21) {
       int r = 0;
@@ -90,6 +88,21 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
 // ---------------------------------------------------------------------------------------------
 constexpr int ASM_LANES = 8;
 
+// sum of the S split partials of one entry, eight loads in flight, added in split order (fp64)
+__device__ __forceinline__ double sum_splits(const float* __restrict__ src, int64_t st, int S) {
+  double t = 0.0;
+  int s = 0;
+  for (; s + 8 <= S; s += 8) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (s + u) * st);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) t += double(v[u]);
+  }
+  for (; s < S; ++s) t += double(__ldcg(src + s * st));
+  return t;
+}
+
 // gathers of one 6x6 block entry: items i0+il, i0+il+nl, ... (fp64 sums: S = H - E Q E^T cancels several
 // digits, so the only roundings kept are those of the fp32 partials themselves and the final store)
 __device__ __forceinline__ void gather_block(const Item* __restrict__ items, int i0, int i1, int il, int nl, int ent,
@@ -103,10 +116,7 @@ __device__ __forceinline__ void gather_block(const Item* __restrict__ items, int
     } else {
       const float* src = Spart + int64_t(it.base) * 36 + e;
       const int64_t st = int64_t(it.stride) * 36;
-      double t = 0.0;
-#pragma unroll 4
-      for (int s = 0; s < S; ++s) t += double(__ldcg(src + s * st));
-      ssum += t;
+      ssum += sum_splits(src, st, S);
     }
   }
 }
@@ -172,10 +182,7 @@ k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, 
     } else {
       const float* src = vEpart + int64_t(it.base) * 6 + r;
       const int64_t st = int64_t(it.stride) * 6;
-      double t = 0.0;
-#pragma unroll 4
-      for (int s = 0; s < S; ++s) t += double(__ldcg(src + s * st));
-      esum += t;
+      esum += sum_splits(src, st, S);
     }
   }
   sv[il][r] = vsum;

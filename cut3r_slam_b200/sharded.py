@@ -16,14 +16,16 @@ from . import droid_backends
 
 
 def partition_by_source(ii, nranks, cost="schur"):
-    """Contiguous ranges of sorted(unique(ii)) per rank, balanced on sum_k (deg_k+1)^2 + 8 deg_k
-    (Schur products + linearisation).  Returns [(keyframes [m_r], edge_index [E_r])] per rank; edge
+    """Contiguous ranges of sorted(unique(ii)) per rank, balanced on the measured per-keyframe
+    linearisation cost.  Returns [(keyframes [m_r], edge_index [E_r])] per rank; edge
     order inside a shard is the original order; eta rows of a shard are the contiguous slice
     [first_slot, first_slot + m_r) of the global eta."""
     ii = ii.cpu()
     kx, kk = torch.unique(ii, return_inverse=True)
     deg = torch.bincount(kk, minlength=kx.numel()).double()
-    w = (deg + 1) ** 2 + 8 * deg if cost == "schur" else deg
+    # measured kernel costs per pixel tile (csrc/dba_api.cu prepare_plan): tcgen05 path deg + 6 up to out-degree
+    # 20, SIMT path 0.064 (deg+1)^2 on a whole SM (two CTA slots) beyond
+    w = torch.where(deg <= 20, deg + 6, 0.128 * (deg + 1) ** 2) if cost == "schur" else deg
     cum = torch.cumsum(w, 0)
     total = float(cum[-1]) if cum.numel() else 0.0
     bounds = [0]
