@@ -44,6 +44,21 @@ def linearize_bytes(E, HW, M):
     return 20 * E * HW + 12 * M * HW
 
 
+def workload_string(name, cfg, p):
+    return (f"{name}: {cfg['P']} keyframes, {cfg['E']} edges, {cfg['ht']}x{cfg['wd']} grid, "
+            f"{p.iterations} LM iterations per ba call, lm={p.lm}, ep={p.ep}, t0={p.t0}")
+
+
+def measured_traffic(name, world):
+    """DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/linearize_traffic.json), or None when there is none for this workload / GPU count."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "linearize_traffic.json")))
+        return rec.get(f"{name}@{world}")
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """Polls SM clock + throttle reasons through NVML while the timed region runs."""
 
@@ -132,8 +147,8 @@ def run_reference(args, rank):
         "impl": "reference", "metric": "ba_edge_pixels_per_s", "value": val, "unit": "edge-pixels/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{WORKLOAD}: {cfg['P']} keyframes, {cfg['E']} edges, {cfg['ht']}x{cfg['wd']} grid, "
-                               f"{cfg['iters']} LM iterations per ba call", "sample": sample},
+        "config": {"workload": workload_string(WORKLOAD, cfg, p), "parallelism": "host CPU, all threads",
+                   "sample": sample},
         "ba_iters_per_s": 1.0 / dt,
         "cpu_baseline": {"value": val, "unit": "edge-pixels/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "edge-pixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -295,8 +310,7 @@ def main():
             "metric": "ba_edge_pixels_per_s", "value": ep_per_s, "unit": "edge-pixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {cfg['P']} keyframes, {cfg['E']} edges, {cfg['ht']}x{cfg['wd']} grid, "
-                                   f"{iters} LM iterations per ba call, lm={p.lm}, ep={p.ep}, t0={p.t0}",
+            "config": {"workload": workload_string(args.workload, cfg, p),
                        "parallelism": f"edges sharded by source keyframe over {world} GPU(s)" if world > 1 else "1 GPU",
                        "l2": "256 MB buffer written between timed steps (inputs 106 MB < 126 MB L2)"},
             "ba_iters_per_s": iters / (ms_step * 1e-3),
@@ -307,7 +321,7 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "k_linearize (residual/Jacobian/Hessian + Schur, fused)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": lin_bytes,
-                         "ms_per_launch": lin_ms, "traffic": None,
+                         "ms_per_launch": lin_ms, "traffic": measured_traffic(args.workload, world),
                          "whole_iteration": {"algorithmic_bytes": b_alg, "achieved": whole, "frac": whole / peak,
                                              "frac_of_8TBs_nominal": whole / 8000.0}},
             "stage_ms_per_lm_iteration": stage_ms,

@@ -99,7 +99,8 @@ struct dba_ctx {
   DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep;
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
-  bool opt_tc = true;                // Schur products on tcgen05 where the out-degree allows
+  bool opt_tc = true;
+  bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
   int64_t* h_idx = nullptr;
   size_t h_idx_cap = 0;
@@ -378,7 +379,9 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");
     mark();
-    if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol)
+    if (ctx->opt_small && g.n6 <= cholesky_small_max_n())
+      CK(launch_cholesky_small(ws, g.n6, st), "cholesky (single CTA)");
+    else if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol)
       CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st), "cholesky (cooperative)");
     else
       CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
@@ -471,6 +474,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
   else if (n == "tensor_cores") { ctx->opt_tc = value != 0; ctx->plan_valid = false; }
+  else if (n == "small_system") ctx->opt_small = value != 0;
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {

@@ -20,13 +20,11 @@ __device__ __forceinline__ double sum_splits(const float* __restrict__ src, int6
 
 // one warp per edge: lanes 0..26 sum the split partials (fp64: a handful of adds, removes one layer of
 // fp32 rounding), the 4 x 36 + 2 x 6 outputs are spread over the lanes
-__global__ void __launch_bounds__(32 * EF_WARPS)
-k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci, const int32_t* __restrict__ cj,
-                const float* __restrict__ Hpart, int E, int S, float* __restrict__ Hblk, float* __restrict__ vblk) {
-  __shared__ float sH[EF_WARPS][36], sHij[EF_WARPS][36], sAd[EF_WARPS][36], sv[EF_WARPS][8];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int c = blockIdx.x * EF_WARPS + warp;
-  if (c >= E) return;
+// one warp finalises edge c: sH / sHij / sAd [36], sv [8] are the warp's shared scratch
+__device__ __forceinline__ void edge_finalize_warp(const float* __restrict__ poses, const int32_t* __restrict__ ci,
+                                                   const int32_t* __restrict__ cj, const float* __restrict__ Hpart, int S,
+                                                   float* __restrict__ Hblk, float* __restrict__ vblk, int c, int lane,
+                                                   float* sH, float* sHij, float* sAd, float* sv) {
   {
     const float hv = float(sum_splits(Hpart + int64_t(c) * S * 32 + lane, 32, S));
     // lane l < 21 holds H[r][cc] with l = r(r+1)/2 + cc (cc <= r); lanes 21..26 hold vj
@@ -34,10 +32,10 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
       int r = 0;
       while ((r + 1) * (r + 2) / 2 <= lane) ++r;
       const int cc = lane - r * (r + 1) / 2;
-      sH[warp][r * 6 + cc] = hv;
-      sH[warp][cc * 6 + r] = hv;
+      sH[r * 6 + cc] = hv;
+      sH[cc * 6 + r] = hv;
     } else if (lane < 27) {
-      sv[warp][lane - 21] = hv;
+      sv[lane - 21] = hv;
     }
   }
   if (lane == 31) {      // an otherwise idle lane builds the adjoint of the edge's relative pose
@@ -45,11 +43,11 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
     relative_pose_Rt(poses, ci[c], cj[c], Rt);
     adjoint_from_Rt(Rt, AdR);
 #pragma unroll
-    for (int i = 0; i < 36; ++i) sAd[warp][i] = AdR[i];
+    for (int i = 0; i < 36; ++i) sAd[i] = AdR[i];
   }
   __syncwarp();
-  const float* H = sH[warp];
-  const float* Ad = sAd[warp];
+  const float* H = sH;
+  const float* Ad = sAd;
   float* out = Hblk + int64_t(c) * 144;
   for (int e = lane; e < 36; e += 32) {          // Hij = -Ad^T Hjj ; Hji = -Hjj Ad ; Hjj
     const int r = e / 6, cc = e - r * 6;
@@ -59,7 +57,7 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
       a += Ad[t * 6 + r] * H[t * 6 + cc];
       hji += H[r * 6 + t] * Ad[t * 6 + cc];
     }
-    sHij[warp][e] = -a;
+    sHij[e] = -a;
     out[1 * 36 + e] = -a;
     out[2 * 36 + e] = -hji;
     out[3 * 36 + e] = H[e];
@@ -69,16 +67,26 @@ k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci,
     const int r = e / 6, cc = e - r * 6;
     float hii = 0.f;
 #pragma unroll
-    for (int t = 0; t < 6; ++t) hii += sHij[warp][r * 6 + t] * Ad[t * 6 + cc];
+    for (int t = 0; t < 6; ++t) hii += sHij[r * 6 + t] * Ad[t * 6 + cc];
     out[e] = -hii;
   }
   if (lane < 6) {
     float a = 0.f;
 #pragma unroll
-    for (int t = 0; t < 6; ++t) a += Ad[t * 6 + lane] * sv[warp][t];
+    for (int t = 0; t < 6; ++t) a += Ad[t * 6 + lane] * sv[t];
     vblk[int64_t(c) * 12 + lane] = -a;                   // vi = -Ad^T vj
-    vblk[int64_t(c) * 12 + 6 + lane] = sv[warp][lane];   // vj
+    vblk[int64_t(c) * 12 + 6 + lane] = sv[lane];   // vj
   }
+}
+
+__global__ void __launch_bounds__(32 * EF_WARPS)
+k_edge_finalize(const float* __restrict__ poses, const int32_t* __restrict__ ci, const int32_t* __restrict__ cj,
+                const float* __restrict__ Hpart, int E, int S, float* __restrict__ Hblk, float* __restrict__ vblk) {
+  __shared__ float sH[EF_WARPS][36], sHij[EF_WARPS][36], sAd[EF_WARPS][36], sv[EF_WARPS][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * EF_WARPS + warp;
+  if (c >= E) return;
+  edge_finalize_warp(poses, ci, cj, Hpart, S, Hblk, vblk, c, lane, sH[warp], sHij[warp], sAd[warp], sv[warp]);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -515,6 +515,110 @@ k_backsolve_smem(const float* __restrict__ Lm, const float* __restrict__ Ldiag, 
   if (tid == 0) { *fail = 0; *bar = 0u; }
 }
 
+
+// ---- small systems (n <= SMALL_N: the frontend's sliding window): the whole factorisation and both
+// solves in ONE CTA, the matrix resident in shared memory, __syncthreads instead of grid barriers.  Same
+// building blocks as above: register potrf of the 32x32 diagonal block in one warp, one thread per panel
+// row for the triangular solve, L_kk^-1 (a second warp, off the chain) for the backward solve.
+constexpr int SMALL_N = 96;
+constexpr int SMALL_T = 256;
+
+__global__ void __launch_bounds__(SMALL_T)
+k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx, int* __restrict__ fail) {
+  __shared__ CholSmem S;                       // LT / rinv of the current block; P[0] = solved panel (k-major)
+  extern __shared__ __align__(16) float csm[];
+  const int ld = ((n + 3) & ~3) + 4;           // 16-byte aligned rows
+  float* sA = csm;                             // [(n+1)][ld] lower triangle + rhs row n
+  float* sLi = sA + (n + 1) * ld;              // [nkb][32][32] inverses of the diagonal blocks
+  float* xs = sLi + 3 * NB * NB;               // [n + 32] solution
+  __shared__ int sbad;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nkb = (n + NB - 1) / NB;
+  if (tid == 0) sbad = 0;
+  {  // lower triangle + rhs row, every thread's loads independent (one L2 round trip, not one per row)
+    const int tot = (n + 1) * ld;
+#pragma unroll 4
+    for (int e = tid; e < tot; e += SMALL_T) {
+      const int i = e / ld, k = e - i * ld;
+      sA[e] = (k < n && (k <= i || i == n)) ? __ldcg(A + int64_t(i) * ldA + k) : 0.f;
+    }
+  }
+  __syncthreads();
+  for (int kb = 0; kb < nkb; ++kb) {
+    const int k0 = kb * NB, nb = min(NB, n - k0), r0 = k0 + nb;
+    if (warp == 0) {                           // ---- diagonal block
+      float a[NB];
+#pragma unroll
+      for (int c = 0; c < NB; ++c) a[c] = (lane < nb && c < nb) ? sA[(k0 + lane) * ld + k0 + c] : ((c == lane) ? 1.f : 0.f);
+      const bool bad = potrf32_warp(a, lane, &S.P[1][0][0]);
+#pragma unroll
+      for (int c = 0; c < NB; ++c) {
+        const float v = (c <= lane) ? a[c] : 0.f;
+        S.LT[c][lane] = v;
+        if (lane < nb && c < nb && c <= lane) sA[(k0 + lane) * ld + k0 + c] = v;
+      }
+      __syncwarp();
+      S.rinv[lane] = 1.0f / S.LT[lane][lane];
+      if (bad && lane == 0) sbad = 1;
+    }
+    __syncthreads();
+    const int nrow = n + 1 - r0;               // rows below the block, the rhs row included
+    if (tid < nrow) {                          // ---- panel rows: x L^T = b, one thread per row (<= 65 rows)
+      float b[NB];
+      load_row(b, sA + (r0 + tid) * ld + k0);
+      solve_row(b, S.LT, S.rinv);
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {               // columns past n (last, partial block) are padding
+        S.P[0][j][tid] = (j < nb) ? b[j] : 0.f;
+        if (j < nb) sA[(r0 + tid) * ld + k0 + j] = b[j];
+      }
+    } else if (warp == SMALL_T / 32 - 1) {     // ---- L_kk^-1, column `lane` solves L v = e_lane (off the chain)
+      float b[NB];
+#pragma unroll
+      for (int c = 0; c < NB; ++c) b[c] = (c == lane) ? 1.f : 0.f;
+      solve_row(b, S.LT, S.rinv);
+#pragma unroll
+      for (int j = 0; j < NB; ++j) sLi[kb * NB * NB + j * NB + lane] = b[j];
+    }
+    __syncthreads();
+    // ---- trailing update: rows i >= r0 (rhs row included), columns r0 <= c <= min(i, n-1)
+    for (int e = tid; e < nrow * (n - r0); e += SMALL_T) {
+      const int ri = e / (n - r0), rc = e - ri * (n - r0);
+      if (rc <= ri) {
+        float acc = 0.f;
+#pragma unroll 8
+        for (int m = 0; m < NB; ++m) acc = fmaf(S.P[0][m][ri], S.P[0][m][rc], acc);
+        sA[(r0 + ri) * ld + r0 + rc] -= acc;
+      }
+    }
+    __syncthreads();
+  }
+  // ---- backward solve L^T x = y (y = row n), block by block, one warp
+  if (warp == 0) {
+    for (int i = lane; i < n + NB; i += 32) xs[i] = (i < n) ? sA[n * ld + i] : 0.f;
+    __syncwarp();
+    for (int kb = nkb - 1; kb >= 0; --kb) {
+      const int k0 = kb * NB, nb = min(NB, n - k0), r0 = k0 + nb;
+      float t = (lane < nb) ? xs[k0 + lane] : 0.f;
+      if (lane < nb)
+        for (int r = r0; r < n; ++r) t = fmaf(-sA[r * ld + k0 + lane], xs[r], t);   // column k0+lane of L below the block
+      __syncwarp();
+      xs[k0 + lane] = (lane < nb) ? t : 0.f;
+      __syncwarp();
+      const float* Li = sLi + kb * NB * NB;
+      float x = 0.f;
+#pragma unroll
+      for (int r = 0; r < NB; ++r) x = fmaf(Li[r * NB + lane], xs[k0 + r], x);
+      __syncwarp();
+      if (lane < nb) xs[k0 + lane] = x;
+      __syncwarp();
+    }
+    const bool bad = sbad != 0;
+    for (int i = lane; i < n; i += 32) dx[i] = bad ? 0.f : xs[i];      // chol.py:14-18: failed factorisation -> zeros
+    if (lane == 0) *fail = 0;
+  }
+}
+
 }  // namespace
 
 #ifdef DBA_CHOL_TRACE
@@ -545,6 +649,18 @@ cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaS
     const size_t smem = size_t(2 * NB * NB + n + NB) * sizeof(float);
     k_backsolve<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, fail, bar, dx);
   }
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+int cholesky_small_max_n() { return SMALL_N; }
+
+cudaError_t launch_cholesky_small(const Workspace& ws, int n, cudaStream_t st) {
+  const int ld = ((n + 3) & ~3) + 4;
+  const size_t smem = (size_t(n + 1) * ld + 3 * NB * NB + n + NB) * sizeof(float);
+  cudaError_t err = cudaFuncSetAttribute(k_chol_small, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+  if (err != cudaSuccess) return err;
+  k_chol_small<<<1, SMALL_T, smem, st>>>(ws.A, ws.ldA, n, ws.dx, ws.fail);
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -70,6 +70,9 @@ int linearize_pick_ppl(int degmax, int nblkmax, bool motion_only, int HW, size_t
 
 cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float lm, float ep,
                             float hscale_lm, bool motion_only, bool block_diag_quirk, cudaStream_t st);
+// n6 <= cholesky_small_max_n(): factorisation + both solves in ONE single-CTA launch (frontend windows)
+cudaError_t launch_cholesky_small(const Workspace& ws, int n6, cudaStream_t st);
+int cholesky_small_max_n();
 cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
 // single cooperative launch (one grid barrier per block step); max_ctas from cholesky_coop_max_ctas (0 = unavailable)
 cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st);
