@@ -129,12 +129,48 @@ __device__ __forceinline__ void gather_block(const Item* __restrict__ items, int
   }
 }
 
+// rhs row of the augmented system: v - E Q w for pose a.  16 item lanes x 6 entries (threads >= 96 of the
+// CTA only take part in the barrier); runs as the trailing CTAs of k_assemble_S.
+constexpr int RHS_LANES = 16;
+
+__device__ __forceinline__ void assemble_rhs_cta(int a, const int32_t* __restrict__ off, const Item* __restrict__ items,
+                                                 const float* __restrict__ vblk, const float* __restrict__ vEpart,
+                                                 int S, int Pp, float* __restrict__ A, int ldA) {
+  __shared__ double sv[RHS_LANES][6], se[RHS_LANES][6];
+  const int il = threadIdx.x / 6, r = threadIdx.x % 6;
+  const bool active = il < RHS_LANES;
+  double vsum = 0.0, esum = 0.0;
+  if (active) {
+    for (int i = off[a] + il; i < off[a + 1]; i += RHS_LANES) {
+      const Item it = items[i];
+      if ((it.flags & 1) == 0) {
+        vsum += double(__ldcg(vblk + int64_t(it.base) * 6 + r));
+      } else {
+        esum += sum_splits(vEpart + int64_t(it.base) * 6 + r, int64_t(it.stride) * 6, S);
+      }
+    }
+    sv[il][r] = vsum;
+    se[il][r] = esum;
+  }
+  __syncthreads();
+  if (il != 0) return;
+#pragma unroll
+  for (int l = 1; l < RHS_LANES; ++l) { vsum += sv[l][r]; esum += se[l][r]; }
+  A[int64_t(6 * Pp) * ldA + a * 6 + r] = float(vsum - esum);
+}
+
 // CTAs [0, nlightCTA): 8 light blocks (<= 8 items) per CTA, one thread per entry; the remaining CTAs: one
 // heavy block (diagonal blocks carry ~50 items) with 8 item lanes per entry, summed in lane order.
 __global__ void __launch_bounds__(36 * ASM_LANES)
 k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, const int32_t* __restrict__ blist,
              int nlight, int nlightCTA, const float* __restrict__ Hblk, const float* __restrict__ Spart, int S,
-             float lm, float ep, bool block_diag_quirk, float* __restrict__ A, int ldA) {
+             float lm, float ep, bool block_diag_quirk, float* __restrict__ A, int ldA, int nSctas,
+             const int32_t* __restrict__ roff, const Item* __restrict__ ritems, const float* __restrict__ vblk,
+             const float* __restrict__ vEpart, int Pp) {
+  if (int(blockIdx.x) >= nSctas) {               // trailing CTAs: one pose of the rhs row each
+    assemble_rhs_cta(blockIdx.x - nSctas, roff, ritems, vblk, vEpart, S, Pp, A, ldA);
+    return;
+  }
   __shared__ double sh[ASM_LANES][36], ss[ASM_LANES][36];
   const bool light = int(blockIdx.x) < nlightCTA;
   const int grp = threadIdx.x / 36, ent = threadIdx.x % 36;
@@ -171,35 +207,6 @@ k_assemble_S(const int32_t* __restrict__ off, const Item* __restrict__ items, co
   double val = damp ? hsum + (double(ep) + double(lm) * hsum) : hsum;
   val -= ssum;
   A[int64_t(6 * a + r) * ldA + 6 * b + c] = float(val);
-}
-
-// rhs row of the augmented system: v - E Q w.  One CTA per pose: 16 item lanes x 6 entries.
-constexpr int RHS_LANES = 16;
-
-__global__ void __launch_bounds__(6 * RHS_LANES)
-k_assemble_rhs(const int32_t* __restrict__ off, const Item* __restrict__ items, const float* __restrict__ vblk,
-               const float* __restrict__ vEpart, int S, int Pp, float* __restrict__ A, int ldA) {
-  __shared__ double sv[RHS_LANES][6], se[RHS_LANES][6];
-  const int a = blockIdx.x;
-  const int il = threadIdx.x / 6, r = threadIdx.x % 6;
-  double vsum = 0.0, esum = 0.0;
-  for (int i = off[a] + il; i < off[a + 1]; i += RHS_LANES) {
-    const Item it = items[i];
-    if ((it.flags & 1) == 0) {
-      vsum += double(__ldcg(vblk + int64_t(it.base) * 6 + r));
-    } else {
-      const float* src = vEpart + int64_t(it.base) * 6 + r;
-      const int64_t st = int64_t(it.stride) * 6;
-      esum += sum_splits(src, st, S);
-    }
-  }
-  sv[il][r] = vsum;
-  se[il][r] = esum;
-  __syncthreads();
-  if (il != 0) return;
-#pragma unroll
-  for (int l = 1; l < RHS_LANES; ++l) { vsum += sv[l][r]; esum += se[l][r]; }
-  A[int64_t(6 * Pp) * ldA + a * 6 + r] = float(vsum - esum);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -316,12 +323,11 @@ cudaError_t launch_assemble(const DeviceGraph& g, const BAInputs& in, const Work
     g_launch_count++;
   }
   const int nlightCTA = (g.n_light + ASM_LANES - 1) / ASM_LANES;
-  k_assemble_S<<<nlightCTA + (g.nSblk - g.n_light), 36 * ASM_LANES, 0, st>>>(
+  const int nSctas = nlightCTA + (g.nSblk - g.n_light);
+  k_assemble_S<<<nSctas + g.Pp, 36 * ASM_LANES, 0, st>>>(
       g.sblk_off, g.sblk_items, g.sblk_list, g.n_light, nlightCTA, ws.Hblk, ws.Spart, g.S, lm, ep, block_diag_quirk,
-      ws.A, ws.ldA);
-  k_assemble_rhs<<<g.Pp, 6 * RHS_LANES, 0, st>>>(g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.S, g.Pp,
-                                                         ws.A, ws.ldA);
-  g_launch_count += 2;
+      ws.A, ws.ldA, nSctas, g.rhs_off, g.rhs_items, ws.vblk, ws.vEpart, g.Pp);
+  g_launch_count += 1;
   return cudaGetLastError();
 }
 
