@@ -189,10 +189,10 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
       const int slots = 2 * sm;
       double best = 1e300;
       // measured (backend graph, 1 GPU): flat optimum for 2..5 waves of CTAs, clearly slower below; so only
-      // split counts that give >= 2.5 waves compete (capped at 2 tiles per CTA), the simulation picks among them
+      // split counts that give >= 3 waves compete (capped at 2 tiles per CTA), the simulation picks among them
       const int njobs = int(degs.size() + 2 * wide.size());
       int cand_lo = 1;
-      while (cand_lo < ntilesT && (ntilesT + cand_lo - 1) / cand_lo > 2 && njobs * cand_lo < (5 * slots) / 2) ++cand_lo;
+      while (cand_lo < ntilesT && (ntilesT + cand_lo - 1) / cand_lo > 2 && njobs * cand_lo < 3 * slots) ++cand_lo;
       for (int cand = cand_lo; cand <= 52 && cand <= ntilesT; ++cand) {
         const int tps_c = (ntilesT + cand - 1) / cand, S_c = (ntilesT + tps_c - 1) / tps_c;
         if (S_c != cand && cand != cand_lo) continue;
