@@ -31,6 +31,10 @@ SIGNATURES = {
     "dba_iproj": (C.c_int, [C.c_void_p, c_f, c_f, c_f, C.c_int64, C.c_int, C.c_int, c_f, C.c_void_p]),
     "dba_depth_filter": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_i, c_f, C.c_int64, C.c_int64, C.c_int, C.c_int, c_f,
                                    C.c_void_p]),
+    "dba_proj_trans": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                 C.c_int64, c_f, c_f, C.c_void_p]),
+    "dba_bi_inter": (C.c_int, [C.c_void_p, c_f, c_f, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, c_f, c_f,
+                               C.c_void_p]),
     "dba_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "dba_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "dba_comm_destroy": (C.c_int, [C.c_void_p]),

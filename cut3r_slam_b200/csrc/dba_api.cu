@@ -106,6 +106,10 @@ struct dba_ctx {
   size_t h_idx_cap = 0;
   // host-entry staging (dba_ba_host)
   DevBuf s_poses, s_disps, s_intr, s_sens, s_targets, s_weights, s_eta, s_ii, s_jj, s_dx, s_dz;
+  // proj_trans: CSR of the edges by source keyframe (cached by the edge lists)
+  std::vector<int64_t> pt_ii, pt_jj;
+  DevBuf d_pt;
+  int pt_M = 0, pt_N = 0;
   // NCCL
   void* comm = nullptr;
   int nranks = 1, rank = 0;
@@ -454,7 +458,7 @@ void dba_destroy(dba_ctx* c) {
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
-                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz};
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
@@ -590,6 +594,74 @@ int dba_depth_filter(dba_ctx* ctx, const float* poses, const float* disps, const
   g_launch_count = 0;
   CK(launch_depth_filter(poses, disps, intrinsics, ix, thresh, K, int(N), ht, wd, out,
                          reinterpret_cast<cudaStream_t>(stream)), "depth_filter");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
+                   const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
+                   int64_t M, float* C_out, float* w_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
+  if (E == 0) return M == 0 ? 0 : fail_arg(ctx, "M must be |unique(ii)|");
+  if (!poses || !disps || !intrinsics || !targets || !weights || !ii || !jj || !C_out || !w_out)
+    return fail_arg(ctx, "NULL argument");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  if (size_t(2 * E) > ctx->h_idx_cap) {
+    if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
+    ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
+    CK(cudaMallocHost(&ctx->h_idx, size_t(2 * E + 64) * sizeof(int64_t)), "pinned staging");
+    ctx->h_idx_cap = size_t(2 * E + 64);
+  }
+  CK(cudaMemcpyAsync(ctx->h_idx, ii, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "ii -> host");
+  CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
+  CK(cudaStreamSynchronize(st), "ii/jj -> host");
+  const int64_t* hi = ctx->h_idx; const int64_t* hj = ctx->h_idx + E;
+  const bool same = int64_t(ctx->pt_ii.size()) == E && ctx->pt_N == int(N) &&
+                    std::memcmp(ctx->pt_ii.data(), hi, E * sizeof(int64_t)) == 0 &&
+                    std::memcmp(ctx->pt_jj.data(), hj, E * sizeof(int64_t)) == 0;
+  if (!same) {   // kx = sorted unique(ii) (ba.py:203), edges of a keyframe in ascending edge id
+    std::vector<int32_t> deg(N, 0);
+    for (int64_t e = 0; e < E; ++e) {
+      if (hi[e] < 0 || hi[e] >= N || hj[e] < 0 || hj[e] >= N) return fail_arg(ctx, "edge index outside the frame buffer");
+      deg[hi[e]]++;
+    }
+    std::vector<int32_t> slot(N, -1), kx, koff(1, 0), cedge(E), cj(E);
+    for (int f = 0; f < int(N); ++f)
+      if (deg[f] > 0) { slot[f] = int32_t(kx.size()); kx.push_back(f); koff.push_back(koff.back() + deg[f]); }
+    std::vector<int32_t> cur(koff.begin(), koff.end() - 1);
+    for (int64_t e = 0; e < E; ++e) { const int c = cur[slot[hi[e]]]++; cedge[c] = int32_t(e); cj[c] = int32_t(hj[e]); }
+    std::vector<int32_t> pack;
+    auto put = [&](const std::vector<int32_t>& v) { pack.insert(pack.end(), v.begin(), v.end()); while (pack.size() % 4) pack.push_back(0); };
+    put(kx); put(koff); put(cedge); put(cj);
+    CK(ctx->d_pt.ensure(pack.size() * 4 + 16), "proj_trans plan");
+    CK(cudaMemcpyAsync(ctx->d_pt.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "proj_trans plan");
+    CK(cudaStreamSynchronize(st), "proj_trans plan");
+    ctx->pt_ii.assign(hi, hi + E); ctx->pt_jj.assign(hj, hj + E);
+    ctx->pt_M = int(kx.size()); ctx->pt_N = int(N);
+  }
+  if (M != ctx->pt_M) return fail_arg(ctx, "C / w must hold one map per unique source keyframe (M != |unique(ii)|)");
+  auto r4 = [](size_t n) { return (n + 3) & ~size_t(3); };
+  const int32_t* base = ctx->d_pt.as<int32_t>();
+  const int32_t* kx = base; const int32_t* koff = kx + r4(size_t(M)); const int32_t* cedge = koff + r4(size_t(M) + 1);
+  const int32_t* cj = cedge + r4(size_t(E));
+  g_launch_count = 0;
+  CK(launch_proj_trans(poses, disps, intrinsics, targets, weights, kx, koff, cedge, cj, int(M), ht * wd, wd, C_out, w_out, st),
+     "proj_trans");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_bi_inter(dba_ctx* ctx, const float* scales, const float* grid, int64_t M, int ht, int wd, int hs, int ws,
+                 float* vals_out, float* J_out, void* stream) {
+  if (!ctx) return -1;
+  if (M < 0 || ht <= 0 || wd <= 0 || hs <= 0 || ws <= 0) return fail_arg(ctx, "negative or zero size");
+  if (M == 0) return 0;
+  if (!scales || !grid || !vals_out || !J_out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_bi_inter(scales, grid, int(M), ht * wd, hs, ws, vals_out, J_out, reinterpret_cast<cudaStream_t>(stream)), "bi_inter");
   ctx->last_launches = g_launch_count;
   return 0;
 }

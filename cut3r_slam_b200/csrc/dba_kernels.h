@@ -93,4 +93,11 @@ cudaError_t launch_depth_filter(const float* poses, const float* disps, const fl
                                 const float* thresh, int64_t K, int N, int ht, int wd, float* out,
                                 cudaStream_t st);
 
+// JDSA path (dba_jdsa.cu)
+cudaError_t launch_proj_trans(const float* poses, const float* disps, const float* intr, const float* targets,
+                              const float* weights, const int32_t* kx, const int32_t* koff, const int32_t* cedge,
+                              const int32_t* cj, int M, int HW, int wd, float* Cout, float* wout, cudaStream_t st);
+cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int HW, int hs, int ws, float* vals,
+                            float* J, cudaStream_t st);
+
 }  // namespace dba

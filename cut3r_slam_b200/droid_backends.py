@@ -221,6 +221,54 @@ def depth_filter(poses, disps, intrinsics, ix, thresh):
     return out
 
 
+def proj_trans(poses, disps, intrinsics, targets, weights, ii, jj):
+    """droid_backends.proj_trans(poses, disps, intrinsics, target, weight, ii, jj) -> (C, w)
+    (hislam2/geom/ba.py:200).  C, w [M,ht,wd] with M = |unique(ii)|, rows in sorted(unique(ii)) order."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(targets, "targets", torch.float32, 4)
+    _check(weights, "weights", torch.float32, 4)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if jj.numel() != E:
+        raise RuntimeError("ii and jj must have the same length")
+    for t, nm in ((targets, "targets"), (weights, "weights")):
+        if tuple(t.shape) != (E, 2, ht, wd):
+            raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
+    M = int(torch.unique(ii).numel())
+    Cm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+    wm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_proj_trans(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(targets),
+                                         _ptr(weights), _ptr(ii), _ptr(jj), E, N, ht, wd, M, _ptr(Cm), _ptr(wm),
+                                         C.c_void_p(stream)))
+    return Cm, wm
+
+
+def bi_inter(scales, grid):
+    """droid_backends.bi_inter(scales, grid) -> (vals, J)  (hislam2/geom/ba.py:167): scales [M,hs,ws],
+    grid [M,ht,wd,2] (x along ws, y along hs, node units); vals [M,ht,wd], J [M,ht,wd,hs*ws]."""
+    _check(scales, "scales", torch.float32, 3)
+    _check(grid, "grid", torch.float32, 4)
+    M, hs, ws = scales.shape
+    if grid.shape[0] != M or grid.shape[3] != 2:
+        raise RuntimeError(f"grid must be [{M},ht,wd,2], got {tuple(grid.shape)}")
+    ht, wd = grid.shape[1], grid.shape[2]
+    vals = torch.empty((M, ht, wd), dtype=torch.float32, device=scales.device)
+    J = torch.empty((M, ht, wd, hs * ws), dtype=torch.float32, device=scales.device)
+    ctx = context(scales.device)
+    with torch.cuda.device(scales.device):
+        stream = torch.cuda.current_stream(scales.device).cuda_stream
+        ctx.check(ctx.lib.dba_bi_inter(ctx.handle, _ptr(scales), _ptr(grid), M, ht, wd, hs, ws, _ptr(vals), _ptr(J),
+                                       C.c_void_p(stream)))
+    return vals, J
+
+
 def debug_system(device=None):
     """(S_lower [n6,n6], rhs [n6]) of the last iteration's reduced system (needs keep_system=1)."""
     ctx = context(device)

@@ -77,6 +77,18 @@ int dba_depth_filter(dba_ctx* ctx, const float* poses, const float* disps, const
                      const int64_t* ix, const float* thresh, int64_t K, int64_t N, int ht, int wd, float* out,
                      void* stream);
 
+/* ---- JDSA ops (hislam2/geom/ba.py:161-241, the use_mono branch of cuda_ba)
+ * proj_trans(poses, disps, intrinsics, target, weight, ii, jj) -> (C, w)  [hislam2/geom/ba.py:200]:
+ *   C, w [M,ht,wd], rows in sorted(unique(ii)) order: C = sum over the keyframe's edges and the two residual rows
+ *   of w Jz^2, w = sum w r Jz (ba.py:62-68,83-90, without eta); targets / weights [E,2,ht,wd]. */
+int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
+                   const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
+                   int64_t M, float* C_out, float* w_out, void* stream);
+/* bi_inter(scales, grid) -> (vals, J)  [hislam2/geom/ba.py:167]: scales [M,hs,ws], grid [M,ht,wd,2] = (x along ws,
+ *   y along hs) in node units; vals [M,ht,wd] bilinear samples, J [M,ht,wd,hs*ws] their Jacobian w.r.t. scales[m]. */
+int dba_bi_inter(dba_ctx* ctx, const float* scales, const float* grid, int64_t M, int ht, int wd, int hs, int ws,
+                 float* vals_out, float* J_out, void* stream);
+
 /* ---- sharded global BA (no reference counterpart: SURVEY.md section 8e).  Edges are partitioned by
  * source keyframe ii across ranks; each rank calls dba_ba with ITS edges/targets/weights/eta and a
  * full replica of poses; the reduced system is summed with one ncclAllReduce per iteration. */
