@@ -109,7 +109,9 @@ struct dba_ctx {
   // proj_trans: CSR of the edges by source keyframe (cached by the edge lists)
   std::vector<int64_t> pt_ii, pt_jj;
   DevBuf d_pt;
+  DevBuf d_jd;                 // proj_trans outputs inside dba_jdsa
   int pt_M = 0, pt_N = 0;
+  bool pt_contig = true;       // unique(ii) is a contiguous range of frames
   // NCCL
   void* comm = nullptr;
   int nranks = 1, rank = 0;
@@ -458,7 +460,7 @@ void dba_destroy(dba_ctx* c) {
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
-                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt};
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
@@ -598,16 +600,11 @@ int dba_depth_filter(dba_ctx* ctx, const float* poses, const float* disps, const
   return 0;
 }
 
-int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
-                   const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
-                   int64_t M, float* C_out, float* w_out, void* stream) {
-  if (!ctx) return -1;
-  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
-  if (E == 0) return M == 0 ? 0 : fail_arg(ctx, "M must be |unique(ii)|");
-  if (!poses || !disps || !intrinsics || !targets || !weights || !ii || !jj || !C_out || !w_out)
-    return fail_arg(ctx, "NULL argument");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+// the per-source-keyframe edge lists of proj_trans (cached by (ii, jj)) + its launch; *kx_out = device kx [M]
+static int proj_trans_run(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                          const float* targets, const float* weights, const int64_t* ii, const int64_t* jj, int64_t E,
+                          int64_t N, int ht, int wd, int64_t M, float* C_out, float* w_out, cudaStream_t st,
+                          const int32_t** kx_out) {
   if (size_t(2 * E) > ctx->h_idx_cap) {
     if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
     ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
@@ -640,15 +637,68 @@ int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const f
     CK(cudaStreamSynchronize(st), "proj_trans plan");
     ctx->pt_ii.assign(hi, hi + E); ctx->pt_jj.assign(hj, hj + E);
     ctx->pt_M = int(kx.size()); ctx->pt_N = int(N);
+    ctx->pt_contig = kx.back() - kx.front() + 1 == int32_t(kx.size());
   }
   if (M != ctx->pt_M) return fail_arg(ctx, "C / w must hold one map per unique source keyframe (M != |unique(ii)|)");
   auto r4 = [](size_t n) { return (n + 3) & ~size_t(3); };
   const int32_t* base = ctx->d_pt.as<int32_t>();
   const int32_t* kx = base; const int32_t* koff = kx + r4(size_t(M)); const int32_t* cedge = koff + r4(size_t(M) + 1);
   const int32_t* cj = cedge + r4(size_t(E));
-  g_launch_count = 0;
   CK(launch_proj_trans(poses, disps, intrinsics, targets, weights, kx, koff, cedge, cj, int(M), ht * wd, wd, C_out, w_out, st),
      "proj_trans");
+  if (kx_out) *kx_out = kx;
+  return 0;
+}
+
+int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
+                   const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
+                   int64_t M, float* C_out, float* w_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
+  if (E == 0) return M == 0 ? 0 : fail_arg(ctx, "M must be |unique(ii)|");
+  if (!poses || !disps || !intrinsics || !targets || !weights || !ii || !jj || !C_out || !w_out)
+    return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  const int rc = proj_trans_run(ctx, poses, disps, intrinsics, targets, weights, ii, jj, E, N, ht, wd, M, C_out, w_out,
+                                reinterpret_cast<cudaStream_t>(stream), nullptr);
+  ctx->last_launches = g_launch_count;
+  return rc;
+}
+
+int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrinsics, const float* disps_prior,
+             float* dscales, const float* targets, const float* weights, const float* eta, const int64_t* ii,
+             const int64_t* jj, int64_t E, int64_t N, int ht, int wd, int hs, int ws, int64_t M, float alpha, float ep,
+             float lm, float* dzcov_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || hs <= 0 || ws <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
+  if (hs * ws > jdsa_max_nodes()) return fail_arg(ctx, "scale grid larger than 64 nodes per keyframe");
+  if (E == 0) return M == 0 ? 0 : fail_arg(ctx, "M must be |unique(ii)|");
+  if (!poses || !disps || !intrinsics || !disps_prior || !dscales || !targets || !weights || !eta || !ii || !jj || !dzcov_out)
+    return fail_arg(ctx, "NULL argument");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  const size_t HW = size_t(ht) * wd;
+  const size_t nD = size_t(N) * size_t(hs * ws), nZ = size_t(N) * HW;
+  CK(ctx->d_jd.ensure((2 * size_t(M) * HW + nZ + nD) * sizeof(float) + 16), "JDSA scratch");
+  float* Cm = ctx->d_jd.as<float>();
+  float* wm = Cm + size_t(M) * HW;
+  g_launch_count = 0;
+  const int32_t* kx = nullptr;
+  const int rc = proj_trans_run(ctx, poses, disps, intrinsics, targets, weights, ii, jj, E, N, ht, wd, M, Cm, wm, st, &kx);
+  if (rc != 0) return rc;
+  const float* disps_in = disps;
+  const float* scales_in = dscales;
+  if (!ctx->pt_contig) {
+    // a hole in unique(ii): slots read the prior terms of OTHER keyframes (see k_jdsa), which other CTAs update --
+    // give every CTA the values from before the step, as the reference's out-of-place tensors do
+    float* snap = wm + size_t(M) * HW;
+    CK(cudaMemcpyAsync(snap, disps, nZ * sizeof(float), cudaMemcpyDeviceToDevice, st), "JDSA snapshot");
+    CK(cudaMemcpyAsync(snap + nZ, dscales, nD * sizeof(float), cudaMemcpyDeviceToDevice, st), "JDSA snapshot");
+    disps_in = snap; scales_in = snap + nZ;
+  }
+  CK(launch_jdsa(disps, Cm, wm, eta, disps_prior, dscales, disps_in, scales_in, kx, int(M), int(N), ht, wd, hs, ws, alpha,
+                 ep, lm, dzcov_out, nullptr, nullptr, st), "jdsa");
   ctx->last_launches = g_launch_count;
   return 0;
 }

@@ -94,6 +94,213 @@ k_bi_inter(const float* __restrict__ scales, const float* __restrict__ grid, int
   Jp[y1 * ws + x1] += w11;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// One JDSA step per source keyframe (ba.py:203-239 + chol.py:80-108), one CTA each.  Because Hs, Es, vs are
+// scattered at (kx, kx) only, the reduced system is M independent D x D problems (D = hs*ws <= 64):
+//   g = -m prior ;  Jso_a = g h_a(p)  (h_a = bilinear weight of node a at pixel p, 4 non-zero per pixel)
+//   C' = C + m alpha + (1-m) eta ; w' = w - m alpha rd ; rd = disp - prior * bilinear(scales) ; Q = 1/C'
+//   S = alpha T1 (1 + lm I) + ep I - alpha^2 T2,  T1 = sum g^2 h_a h_b, T2 = sum Q g^2 h_a h_b
+//   v = -alpha sum g h_a rd - alpha sum g h_a Q w'
+//   dso = S^-1 v ; dz = Q (w' - alpha sum_a Jso_a dso_a) ; dzcov = u^T S^-1 u + Q, u_a = alpha Jso_a Q
+// All sums are lane-strided partials + a fixed shuffle tree (deterministic).
+// ---------------------------------------------------------------------------------------------
+constexpr int JD_T = 256;
+constexpr int JD_DMAX = 64;
+
+struct PixNodes { int a[4]; float h[4]; };
+
+__device__ __forceinline__ PixNodes pix_nodes(float gx, float gy, int hs, int ws) {
+  int x0 = int(floorf(gx)), y0 = int(floorf(gy));
+  x0 = max(0, min(x0, ws - 2 >= 0 ? ws - 2 : 0));
+  y0 = max(0, min(y0, hs - 2 >= 0 ? hs - 2 : 0));
+  const int x1 = min(x0 + 1, ws - 1), y1 = min(y0 + 1, hs - 1);
+  const float wx = gx - float(x0), wy = gy - float(y0);
+  PixNodes n;
+  n.a[0] = y0 * ws + x0; n.a[1] = y0 * ws + x1; n.a[2] = y1 * ws + x0; n.a[3] = y1 * ws + x1;
+  n.h[0] = (1.f - wy) * (1.f - wx); n.h[1] = (1.f - wy) * wx; n.h[2] = wy * (1.f - wx); n.h[3] = wy * wx;
+  return n;
+}
+
+__device__ __forceinline__ float node_weight(const PixNodes& n, int a) {
+  return (n.a[0] == a ? n.h[0] : 0.f) + (n.a[1] == a ? n.h[1] : 0.f) + (n.a[2] == a ? n.h[2] : 0.f) +
+         (n.a[3] == a ? n.h[3] : 0.f);
+}
+
+__global__ void __launch_bounds__(JD_T)
+k_jdsa(float* disps, const float* disps_in, const float* __restrict__ Cin, const float* __restrict__ win,
+       const float* __restrict__ eta, const float* __restrict__ prior, float* scales, const float* scales_in,
+       const int32_t* __restrict__ kx, int M, int ht, int wd, int hs, int ws, float alpha, float ep, float lm, float* __restrict__ dzcov, float* __restrict__ dz_out,
+       float* __restrict__ dso_out) {
+  __shared__ float sS[JD_DMAX][JD_DMAX + 1], sInv[JD_DMAX][JD_DMAX + 1], sv[JD_DMAX], sdso[JD_DMAX], ssc[JD_DMAX],
+      ssc_src[JD_DMAX];
+  __shared__ int s_found;
+  const int m = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int D = hs * ws, HW = ht * wd;
+  const int k = kx[m];
+  // ba.py:163: torch.linspace(0, hs-1-1e-6, ht) / (0, ws-1-1e-6, wd) in fp32, torch's symmetric evaluation
+  const float endy = float(hs - 1) - 1e-6f, endx = float(ws - 1) - 1e-6f;
+  const float stepy = ht > 1 ? endy / float(ht - 1) : 0.f, stepx = wd > 1 ? endx / float(wd - 1) : 0.f;
+  // ba.py:218-225: the prior blocks Hs, Es, vs of keyframe kx[q] are scattered at slot kx[q] - kx[0], not at q, and
+  // slots >= M are dropped.  Slot m therefore takes its prior terms from frame ks = kx[0] + m IF that frame is a
+  // source keyframe (ks == k whenever unique(ii) is a contiguous range -- the normal case), else it has none;
+  // C, w, eta, the retraction and dso -> dscales[kx[m]] stay with slot m's own keyframe.
+  const int ks = kx[0] + m;
+  if (tid == 0) s_found = 0;
+  __syncthreads();
+  for (int q = tid; q < M; q += JD_T) if (kx[q] == ks) s_found = 1;
+  const float* dk = disps_in + int64_t(k) * HW;
+  const float* pk = prior + int64_t(k) * HW;
+  const float* dsrc = disps_in + int64_t(ks) * HW;
+  const float* psrc = prior + int64_t(ks) * HW;
+  for (int i = tid; i < D; i += JD_T) ssc[i] = scales_in[int64_t(k) * D + i];
+  __syncthreads();
+  const bool has_prior = s_found != 0;
+  for (int i = tid; i < D; i += JD_T) ssc_src[i] = has_prior ? scales_in[int64_t(ks) * D + i] : 0.f;
+  for (int i = tid; i < D * (JD_DMAX + 1); i += JD_T) { (&sS[0][0])[i] = 0.f; (&sInv[0][0])[i] = 0.f; }
+  __syncthreads();
+
+  // per-pixel quantities, recomputed where needed (a few loads each)
+  auto pixel = [&](int p, PixNodes& n, float& g, float& Q, float& wp, float& rd) {
+    const int py = p / wd, px = p - py * wd;
+    const float gy = py < ht / 2 ? stepy * float(py) : endy - stepy * float(ht - 1 - py);
+    const float gx = px < wd / 2 ? stepx * float(px) : endx - stepx * float(wd - 1 - px);
+    n = pix_nodes(gx, gy, hs, ws);
+    const float pr = pk[p], d = dk[p];
+    const float mk = pr > 0.f ? 1.f : 0.f;
+    const float bil = n.h[0] * ssc[n.a[0]] + n.h[1] * ssc[n.a[1]] + n.h[2] * ssc[n.a[2]] + n.h[3] * ssc[n.a[3]];
+    rd = d - pr * bil;
+    const float Cp = Cin[int64_t(m) * HW + p] + mk * alpha + (1.f - mk) * eta[int64_t(m) * HW + p];
+    wp = win[int64_t(m) * HW + p] - mk * alpha * rd;
+    Q = 1.0f / Cp;
+    g = -mk * pr;
+    if (ks != k) {                                         // prior terms of the frame scattered into this slot
+      if (has_prior) {
+        const float ps = psrc[p];
+        const float bs = n.h[0] * ssc_src[n.a[0]] + n.h[1] * ssc_src[n.a[1]] + n.h[2] * ssc_src[n.a[2]] +
+                         n.h[3] * ssc_src[n.a[3]];
+        g = ps > 0.f ? -ps : 0.f;
+        rd = dsrc[p] - ps * bs;
+      } else {
+        g = 0.f;
+      }
+    }
+  };
+
+  // ---- reduced system: one warp per (a, b >= ... ) entry with adjacent nodes, and per rhs entry ----
+  if (has_prior) {
+    const int ntask = D * D + D;                           // (a, b) pairs with b <= a are used; the rest skipped
+    for (int t = warp; t < ntask; t += JD_T / 32) {
+      const bool is_v = t >= D * D;
+      const int a = is_v ? t - D * D : t / D, b = is_v ? a : t % D;
+      if (b > a) continue;
+      const int ya = a / ws, xa = a % ws, yb = b / ws, xb = b % ws;
+      if (abs(ya - yb) > 1 || abs(xa - xb) > 1) continue;  // no pixel sees both nodes
+      float s1 = 0.f, s2 = 0.f;
+      for (int p = lane; p < HW; p += 32) {
+        PixNodes n; float g, Q, wp, rd;
+        pixel(p, n, g, Q, wp, rd);
+        const float ha = node_weight(n, a);
+        if (is_v) { s1 += g * ha * rd; s2 += g * ha * Q * wp; }
+        else { const float hb = node_weight(n, b); const float q = g * g * ha * hb; s1 += q; s2 += Q * q; }
+      }
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+      if (lane == 0) {
+        if (is_v) sv[a] = -alpha * s1 - alpha * s2;
+        else {
+          const float dmp = (a == b) ? 1.f : 0.f;
+          const float val = alpha * s1 + dmp * (ep + lm * alpha * s1) - alpha * alpha * s2;
+          sS[a][b] = val; sS[b][a] = val;
+        }
+      }
+    }
+  } else {
+    for (int i = tid; i < D; i += JD_T) { sS[i][i] = ep; sv[i] = 0.f; }
+  }
+  __syncthreads();
+  // ---- Cholesky of S (lower, in place), warp 0, lanes own rows i and i+32 ----
+  if (warp == 0) {
+    for (int j = 0; j < D; ++j) {
+      const float d = sS[j][j];
+      const float r = d > 0.f ? 1.0f / sqrtf(d) : 0.f;
+      __syncwarp();
+      for (int i = j + lane; i < D; i += 32) sS[i][j] = (i == j) ? d * r : sS[i][j] * r;
+      __syncwarp();
+      for (int i = j + 1 + lane; i < D; i += 32) {
+        const float lij = sS[i][j];
+        for (int c = j + 1; c <= i; ++c) sS[i][c] = fmaf(-lij, sS[c][j], sS[i][c]);
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  // ---- S^-1: every warp solves L L^T x = e_c for its columns c ----
+  for (int c = warp; c < D; c += JD_T / 32) {
+    float* x = &sInv[c][0];                                // row c of the (symmetric) inverse
+    for (int i = lane; i < D; i += 32) x[i] = (i == c) ? 1.f : 0.f;
+    __syncwarp();
+    for (int i = 0; i < D; ++i) {                          // forward: L y = e_c
+      const float yi = x[i] / sS[i][i];
+      __syncwarp();
+      if (lane == 0) x[i] = yi;
+      for (int r = i + 1 + lane; r < D; r += 32) x[r] = fmaf(-sS[r][i], yi, x[r]);
+      __syncwarp();
+    }
+    for (int i = D - 1; i >= 0; --i) {                     // backward: L^T x = y
+      const float xi = x[i] / sS[i][i];
+      __syncwarp();
+      if (lane == 0) x[i] = xi;
+      for (int r = lane; r < i; r += 32) x[r] = fmaf(-sS[i][r], xi, x[r]);
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  for (int a = tid; a < D; a += JD_T) {
+    float s = 0.f;
+    for (int b = 0; b < D; ++b) s = fmaf(sInv[a][b], sv[b], s);
+    sdso[a] = s;
+  }
+  __syncthreads();
+  // ---- per pixel: dz, dzcov, disparity retraction + guards (ba.py:231-239) ----
+  for (int p = tid; p < HW; p += JD_T) {
+    PixNodes n; float g, Q, wp, rd;
+    pixel(p, n, g, Q, wp, rd);
+    float et = 0.f, quad = 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      et += g * n.h[u] * sdso[n.a[u]];
+      float row = 0.f;
+#pragma unroll
+      for (int v = 0; v < 4; ++v) row += n.h[v] * sInv[n.a[u]][n.a[v]];
+      quad += n.h[u] * row;
+    }
+    const float dzv = Q * (wp - alpha * et);
+    const float ua = alpha * g * Q;
+    dzcov[int64_t(m) * HW + p] = ua * ua * quad + Q;
+    if (dz_out != nullptr) dz_out[int64_t(m) * HW + p] = dzv;
+    float nd = dk[p] + dzv;
+    nd = (nd > 10.f) ? 0.f : nd;
+    nd = fmaxf(nd, 0.001f);
+    disps[int64_t(k) * HW + p] = nd;
+  }
+  __syncthreads();                                         // every thread has read ssc / the old disparities
+  for (int i = tid; i < D; i += JD_T) {
+    scales[int64_t(k) * D + i] = ssc[i] + sdso[i];
+    if (dso_out != nullptr) dso_out[int64_t(m) * D + i] = sdso[i];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_guard_all(float* __restrict__ disps, int64_t n) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+    const float v = disps[i];
+    float nd = (v > 10.f) ? 0.f : v;
+    nd = fmaxf(nd, 0.001f);
+    if (nd != v) disps[i] = nd;
+  }
+}
+
 }  // namespace
 
 cudaError_t launch_proj_trans(const float* poses, const float* disps, const float* intr, const float* targets,
@@ -112,6 +319,23 @@ cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int H
   if (M == 0) return cudaSuccess;
   dim3 g((HW + 255) / 256, unsigned(M));
   k_bi_inter<<<g, 256, 0, st>>>(scales, grid, HW, hs, ws, vals, J);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+int jdsa_max_nodes() { return JD_DMAX; }
+
+cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,
+                        float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,
+                        float ep, float lm, float* dzcov, float* dz_out, float* dso_out, cudaStream_t st) {
+  const int HW = ht * wd;
+  if (M > 0) {
+    k_jdsa<<<M, JD_T, 0, st>>>(disps, disps_in, Cin, win, eta, prior, scales, scales_in, kx, M, ht, wd, hs, ws, alpha, ep, lm, dzcov, dz_out,
+                               dso_out);
+    g_launch_count++;
+  }
+  const int64_t n = int64_t(N) * HW;                       // ba.py:238-239 run over the whole disparity tensor
+  k_guard_all<<<unsigned((n + 256 * 8 - 1) / (256 * 8)), 256, 0, st>>>(disps, n);
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -99,5 +99,9 @@ cudaError_t launch_proj_trans(const float* poses, const float* disps, const floa
                               const int32_t* cj, int M, int HW, int wd, float* Cout, float* wout, cudaStream_t st);
 cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int HW, int hs, int ws, float* vals,
                             float* J, cudaStream_t st);
+int jdsa_max_nodes();
+cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,
+                        float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,
+                        float ep, float lm, float* dzcov, float* dz_out, float* dso_out, cudaStream_t st);
 
 }  // namespace dba

@@ -269,6 +269,46 @@ def bi_inter(scales, grid):
     return vals, J
 
 
+def JDSA(target, weight, eta, poses, disps, intrinsics, disps_prior, dscales, ii, jj, alpha=0.01, ep=0.1, lm=1e-4):
+    """hislam2/geom/ba.py:173-241 (`JDSA`, the use_mono branch the factor graph calls between BA iterations) as ONE
+    device step: proj_trans, the mono-prior normal equations, schur_solve_mono_prior (chol.py:80-108, whose keyword
+    defaults are ep / lm here), retraction and the disparity guards.  Same argument order as upstream, batch
+    dimension squeezed like `droid_backends.ba`: target / weight [E,2,ht,wd], eta [M,ht,wd], poses [N,7],
+    disps / disps_prior [N,ht,wd], dscales [N,hs,ws] with hs*ws <= 64.  disps and dscales are updated IN PLACE
+    (upstream returns new tensors: `disps, dscales, cov = JDSA(...)` keeps working); returns (disps, dscales, dzcov)."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(disps_prior, "disps_prior", torch.float32, 3)
+    _check(dscales, "dscales", torch.float32, 3)
+    _check(target, "target", torch.float32, 4)
+    _check(weight, "weight", torch.float32, 4)
+    _check(eta, "eta", torch.float32, 3)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    hs, ws = dscales.shape[1:]
+    if jj.numel() != E:
+        raise RuntimeError("ii and jj must have the same length")
+    if tuple(disps_prior.shape) != (N, ht, wd) or dscales.shape[0] != N:
+        raise RuntimeError("disps_prior / dscales must cover the same frame buffer as disps")
+    for t, nm in ((target, "target"), (weight, "weight")):
+        if tuple(t.shape) != (E, 2, ht, wd):
+            raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
+    M = int(torch.unique(ii).numel())
+    if tuple(eta.shape) != (M, ht, wd):
+        raise RuntimeError(f"eta must be [{M},{ht},{wd}] (one map per unique source keyframe), got {tuple(eta.shape)}")
+    dzcov = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_jdsa(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(disps_prior),
+                                   _ptr(dscales), _ptr(target), _ptr(weight), _ptr(eta), _ptr(ii), _ptr(jj), E, N, ht,
+                                   wd, hs, ws, M, float(alpha), float(ep), float(lm), _ptr(dzcov), C.c_void_p(stream)))
+    return disps, dscales, dzcov
+
+
 def debug_system(device=None):
     """(S_lower [n6,n6], rhs [n6]) of the last iteration's reduced system (needs keep_system=1)."""
     ctx = context(device)

@@ -88,6 +88,16 @@ int dba_proj_trans(dba_ctx* ctx, const float* poses, const float* disps, const f
  *   y along hs) in node units; vals [M,ht,wd] bilinear samples, J [M,ht,wd,hs*ws] their Jacobian w.r.t. scales[m]. */
 int dba_bi_inter(dba_ctx* ctx, const float* scales, const float* grid, int64_t M, int ht, int wd, int hs, int ws,
                  float* vals_out, float* J_out, void* stream);
+/* JDSA(target, weight, eta, poses, disps, intrinsics, disps_sens, dscales, ii, jj, alpha)  [hislam2/geom/ba.py:173-241],
+ *   one joint depth / scale-grid Gauss-Newton step with the poses fixed, in place on disps [N,ht,wd] and dscales
+ *   [N,hs,ws] (hs*ws <= 64): proj_trans, the mono-prior terms (ba.py:205-229), schur_solve_mono_prior
+ *   (hislam2/geom/chol.py:80-108; ep / lm are its keyword defaults 0.1 / 1e-4 upstream), retraction and the two
+ *   disparity guards (ba.py:231-239).  disps_prior [N,ht,wd] (<= 0: no prior at that pixel), eta [M,ht,wd];
+ *   dzcov_out [M,ht,wd] = the depth covariance the reference returns.  M = |unique(ii)|. */
+int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrinsics, const float* disps_prior,
+             float* dscales, const float* targets, const float* weights, const float* eta, const int64_t* ii,
+             const int64_t* jj, int64_t E, int64_t N, int ht, int wd, int hs, int ws, int64_t M, float alpha, float ep,
+             float lm, float* dzcov_out, void* stream);
 
 /* ---- sharded global BA (no reference counterpart: SURVEY.md section 8e).  Edges are partitioned by
  * source keyframe ii across ranks; each rank calls dba_ba with ITS edges/targets/weights/eta and a

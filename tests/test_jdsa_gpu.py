@@ -60,3 +60,96 @@ def test_bi_inter_matches_oracle():
     assert vals.shape == (M, ht, wd) and J.shape == (M, ht, wd, hs * ws)
     assert _rel(vals.cpu(), vr) < 1e-6 and _rel(J.cpu(), Jr) < 1e-6
     assert float((J.sum(-1) - 1).abs().max()) < 1e-6
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the fused JDSA step (dba_jdsa): fp32 on the device against (1) the reference's own fp64 outputs (golden) and
+# (2) the fp64 oracle on cases the golden file does not hold.  Tolerance: 2e-5 relative on the updated disparities,
+# scales and covariance -- the reference's own fp32 run sits 0.7e-6 .. 1.4e-6 from its fp64 run on these cases.
+# ---------------------------------------------------------------------------------------------------------
+JDSA_TOL = 2e-5
+
+
+def _run_jdsa(p, scales, prior, alpha, ii=None, jj=None, targets=None, weights=None, eta=None):
+    db = _db()
+    ii = p.ii if ii is None else ii
+    jj = p.jj if jj is None else jj
+    targets = p.targets if targets is None else targets
+    weights = p.weights if weights is None else weights
+    eta = p.eta if eta is None else eta
+    disps, sc = p.disps.clone().cuda(), scales.clone().cuda()
+    out = db.JDSA(targets.cuda(), weights.cuda(), eta.cuda(), p.poses.cuda(), disps, p.intrinsics.cuda(), prior.cuda(), sc,
+                  ii.cuda(), jj.cuda(), alpha)
+    assert out[0] is disps and out[1] is sc                        # in place, and returned like upstream
+    d = torch.float64
+    ref = oj.JDSA(targets.to(d), weights.to(d), eta.to(d), p.poses.to(d), p.disps.to(d), p.intrinsics.to(d), prior.to(d),
+                  scales.to(d), ii, jj, alpha)
+    return [t.cpu() for t in out], ref
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_jdsa_matches_reference_golden(name):
+    p, scales, prior, alpha = make_case(CASES[name])
+    (disps, sc, dzcov), _ = _run_jdsa(p, scales, prior, alpha)
+    M = dzcov.shape[0]
+    assert _rel(disps, GOLD[f"{name}_disps_f64"]) < JDSA_TOL
+    assert _rel(sc, GOLD[f"{name}_scales_f64"]) < JDSA_TOL
+    assert _rel(dzcov.reshape(M, -1), GOLD[f"{name}_dzcov_f64"]) < JDSA_TOL
+    # the step moved something: not a no-op that happens to sit near the input
+    assert _rel(disps, p.disps) > 1e-3 and _rel(sc, scales) > 1e-4
+
+
+@pytest.mark.parametrize("kw", [
+    dict(P=9, E=40, ht=43, wd=77, iters=1, t0=1, r=3, seed=22, hs=8, ws=8, alpha=0.01),     # 64 nodes, full-size maps
+    dict(P=12, E=60, ht=24, wd=32, iters=1, t0=1, r=3, seed=23, hs=1, ws=5, alpha=0.02),    # degenerate grid rows
+    dict(P=8, E=30, ht=16, wd=20, iters=1, t0=1, r=2, seed=24, hs=4, ws=1, alpha=0.02),
+    dict(P=8, E=30, ht=16, wd=20, iters=1, t0=1, r=2, seed=25, hs=1, ws=1, alpha=0.05),     # one global scale
+])
+def test_jdsa_matches_oracle(kw):
+    p, scales, prior, alpha = make_case(kw)
+    (disps, sc, dzcov), (rd, rs, rc) = _run_jdsa(p, scales, prior, alpha)
+    M = dzcov.shape[0]
+    assert _rel(disps, rd) < JDSA_TOL and _rel(sc, rs) < JDSA_TOL and _rel(dzcov.reshape(M, -1), rc) < JDSA_TOL
+    assert float(disps.min()) >= 0.001 and float(disps.max()) <= 10.0          # ba.py:238-239
+
+
+def test_jdsa_non_contiguous_keyframes_and_guards():
+    """unique(ii) with a hole: upstream scatters the prior blocks of keyframe kx[q] at slot kx[q] - kx[0] (not q) and
+    silently drops slots >= M (ba.py:218-225), while C, w and the retraction go by q.  Slots after the hole therefore
+    pair one keyframe's maps with its predecessor's prior terms, and the slot facing the hole gets no scale update.
+    Reproduced as is.  Also: the guards act on frames that are not source keyframes (whole-tensor torch.where /
+    clamp upstream)."""
+    kw = dict(P=8, E=40, ht=16, wd=20, iters=1, t0=1, r=3, seed=31, hs=2, ws=2, alpha=0.02)
+    p, scales, prior, alpha = make_case(kw)
+    kx_all = torch.unique(p.ii)
+    hole = int(kx_all[2])
+    keep = p.ii != hole
+    eta = p.eta[[i for i, k in enumerate(kx_all.tolist()) if k != hole]]
+    p.disps[hole, 0, :4] = 25.0                                            # > 10 -> 0 -> clamp 1e-3
+    p.disps[hole, 1, :4] = -1.0
+    (disps, sc, dzcov), (rd, rs, rc) = _run_jdsa(p, scales, prior, alpha, ii=p.ii[keep], jj=p.jj[keep],
+                                                targets=p.targets[keep].contiguous(), weights=p.weights[keep].contiguous(),
+                                                eta=eta.contiguous())
+    M = dzcov.shape[0]
+    assert M == kx_all.numel() - 1
+    assert _rel(disps, rd) < JDSA_TOL and _rel(sc, rs) < JDSA_TOL and _rel(dzcov.reshape(M, -1), rc) < JDSA_TOL
+    facing = int(torch.unique(p.ii[keep])[2])                              # slot 2 looks for frame kx[0] + 2 = the hole
+    assert torch.equal(sc[facing], scales[facing]) and torch.equal(sc[hole], scales[hole])
+    assert not torch.equal(sc[int(kx_all[0])], scales[int(kx_all[0])]) and not torch.equal(sc[-1], scales[-1])
+    assert float(disps[hole, 0, :4].max()) == pytest.approx(0.001) and float(disps[hole, 1, :4].max()) == pytest.approx(0.001)
+
+
+def test_jdsa_argument_checks():
+    db = _db()
+    p, scales, prior, alpha = make_case(CASES["a"])
+    g = p.to("cuda")
+    args = lambda **o: [o.get("targets", g.targets), g.weights, o.get("eta", g.eta), g.poses, g.disps.clone(), g.intrinsics,
+                        o.get("prior", prior.cuda()), o.get("scales", scales.cuda()), g.ii, g.jj, alpha]
+    with pytest.raises(RuntimeError):
+        db.JDSA(*args(scales=torch.ones(p.poses.shape[0], 9, 8, device="cuda")))       # > 64 nodes
+    with pytest.raises(RuntimeError):
+        db.JDSA(*args(eta=g.eta[:-1].contiguous()))
+    with pytest.raises(RuntimeError):
+        db.JDSA(*args(prior=prior))                                                    # host tensor
+    with pytest.raises(RuntimeError):
+        db.JDSA(*args(targets=g.targets[:-1].contiguous()))
