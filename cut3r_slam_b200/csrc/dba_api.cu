@@ -716,6 +716,36 @@ int dba_bi_inter(dba_ctx* ctx, const float* scales, const float* grid, int64_t M
   return 0;
 }
 
+int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                  const int64_t* jj, int64_t E, int64_t N, int ht, int wd, float* coords_out, float* valid_out,
+                  void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (E > 65535) return fail_arg(ctx, "more than 65535 edges in one reproject call");
+  if (E == 0) return 0;
+  if (!poses || !disps || !intrinsics || !ii || !jj || !coords_out || !valid_out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_reproject(poses, disps, intrinsics, ii, jj, int(E), ht * wd, wd, coords_out, valid_out,
+                      reinterpret_cast<cudaStream_t>(stream)), "reproject");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_cvx_upsample(dba_ctx* ctx, const float* data, const float* mask, int64_t B, int ht, int wd, int dim,
+                     float* up_out, void* stream) {
+  if (!ctx) return -1;
+  if (B < 0 || ht <= 0 || wd <= 0 || dim <= 0) return fail_arg(ctx, "negative or zero size");
+  if (B > 65535 || ht > 65535) return fail_arg(ctx, "batch or height above 65535");
+  if (B == 0) return 0;
+  if (!data || !mask || !up_out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_cvx_upsample(data, mask, int(B), ht, wd, dim, up_out, reinterpret_cast<cudaStream_t>(stream)), "cvx_upsample");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
 int dba_nccl_unique_id(void* out128) {
   std::string err;
   if (!out128 || !load_nccl(err)) return -1;

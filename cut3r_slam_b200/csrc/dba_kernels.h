@@ -99,6 +99,10 @@ cudaError_t launch_proj_trans(const float* poses, const float* disps, const floa
                               const int32_t* cj, int M, int HW, int wd, float* Cout, float* wout, cudaStream_t st);
 cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int HW, int hs, int ws, float* vals,
                             float* J, cudaStream_t st);
+cudaError_t launch_reproject(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                             const int64_t* jj, int E, int HW, int wd, float* coords, float* valid, cudaStream_t st);
+cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int ht, int wd, int dim, float* up,
+                                cudaStream_t st);
 int jdsa_max_nodes();
 cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,
                         float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,

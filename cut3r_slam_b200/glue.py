@@ -1,0 +1,66 @@
+"""Host-side mirror of the two elementwise steps FactorGraph.update runs either side of `ba`
+(SURVEY.md section 8f rank 2), over `dba_reproject` / `dba_cvx_upsample` (include/dba.h):
+
+  reproject(poses, disps, intrinsics, ii, jj)   DepthVideo.reproject (hislam2/depth_video.pyc @170-178), i.e.
+                                                pops.projective_transform(Gs, disps[None], intrinsics[None], ii, jj)
+                                                (hislam2/geom/projective_ops.py:44-74)
+  cvx_upsample(data, mask), upsample_disp(disp, mask)   hislam2/modules/droid_net.py:21-44
+
+There is no CPU or PyTorch fallback: without libdba.so and a CUDA device these raise.
+"""
+import ctypes as C
+
+import torch
+
+from .droid_backends import _check, _ptr, context
+
+
+def reproject(poses, disps, intrinsics, ii, jj):
+    """-> coords [1,E,ht,wd,2], valid [1,E,ht,wd,1] (the reference's shapes, batch dimension of 1).
+    poses [N,7] (SE3.data), disps [N,ht,wd], intrinsics [4], ii / jj int64 CUDA tensors with values in [0, N)."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if jj.numel() != E:
+        raise RuntimeError("ii and jj must have the same length")
+    if poses.shape[0] < N or poses.shape[1] != 7:
+        raise RuntimeError(f"poses must be [>={N},7], got {tuple(poses.shape)}")
+    coords = torch.empty((1, E, ht, wd, 2), dtype=torch.float32, device=poses.device)
+    valid = torch.empty((1, E, ht, wd, 1), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        for lo in range(0, E, 32768):                      # grid.y limit of one launch
+            n = min(32768, E - lo)
+            ctx.check(ctx.lib.dba_reproject(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ii[lo:lo + n]),
+                                            _ptr(jj[lo:lo + n]), n, N, ht, wd, _ptr(coords[0, lo:lo + n]),
+                                            _ptr(valid[0, lo:lo + n]), C.c_void_p(stream)))
+    return coords, valid
+
+
+def cvx_upsample(data, mask):
+    """data [B,ht,wd,dim], mask [B,576,ht,wd] (any shape with B*576*ht*wd elements in that order) ->
+    [B,8ht,8wd,dim].  `mask` is not modified (upstream writes -inf into its border entries)."""
+    _check(data, "data", torch.float32, 4)
+    _check(mask, "mask", torch.float32)
+    B, ht, wd, dim = data.shape
+    if mask.numel() != B * 576 * ht * wd:
+        raise RuntimeError(f"mask must hold {B}x576x{ht}x{wd} logits, got {tuple(mask.shape)}")
+    up = torch.empty((B, 8 * ht, 8 * wd, dim), dtype=torch.float32, device=data.device)
+    ctx = context(data.device)
+    with torch.cuda.device(data.device):
+        stream = torch.cuda.current_stream(data.device).cuda_stream
+        ctx.check(ctx.lib.dba_cvx_upsample(ctx.handle, _ptr(data), _ptr(mask), B, ht, wd, dim, _ptr(up),
+                                           C.c_void_p(stream)))
+    return up
+
+
+def upsample_disp(disp, mask):
+    """droid_net.py:40-44: disp [B,num,ht,wd], mask [B,num,576,ht,wd] -> [B,num,8ht,8wd]."""
+    _check(disp, "disp", torch.float32, 4)
+    B, num, ht, wd = disp.shape
+    return cvx_upsample(disp.view(B * num, ht, wd, 1), mask).view(B, num, 8 * ht, 8 * wd)

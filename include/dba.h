@@ -99,6 +99,20 @@ int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrin
              const int64_t* jj, int64_t E, int64_t N, int ht, int wd, int hs, int ws, int64_t M, float alpha, float ep,
              float lm, float* dzcov_out, void* stream);
 
+/* ---- the elementwise steps either side of `ba` in FactorGraph.update
+ * reproject(ii, jj) -> (coords, valid)  [hislam2/depth_video.pyc reproject@170-178 = projective_transform,
+ *   hislam2/geom/projective_ops.py:44-74 with jacobian=False]: coords [E,ht,wd,2] = pixel of frame jj[e] that pixel
+ *   (y,x) of frame ii[e] lands on, valid [E,ht,wd,1] = 1 where the transformed depth exceeds MIN_DEPTH = 0.2.
+ *   ii / jj: DEVICE int64 in [0, N) (not validated: no host round trip on this path). */
+int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                  const int64_t* jj, int64_t E, int64_t N, int ht, int wd, float* coords_out, float* valid_out,
+                  void* stream);
+/* cvx_upsample(data, mask) -> up  [hislam2/modules/droid_net.py:21-38; upsample_disp :40-44 is dim = 1]:
+ *   data [B,ht,wd,dim], mask [B,576,ht,wd] (= [B,9,8,8,ht,wd] logits), up [B,8ht,8wd,dim].  `mask` is read-only
+ *   here (the reference writes -inf into the border entries of the caller's tensor as a side effect). */
+int dba_cvx_upsample(dba_ctx* ctx, const float* data, const float* mask, int64_t B, int ht, int wd, int dim,
+                     float* up_out, void* stream);
+
 /* ---- sharded global BA (no reference counterpart: SURVEY.md section 8e).  Edges are partitioned by
  * source keyframe ii across ranks; each rank calls dba_ba with ITS edges/targets/weights/eta and a
  * full replica of poses; the reduced system is summed with one ncclAllReduce per iteration. */
