@@ -110,6 +110,7 @@ struct dba_ctx {
   std::vector<int64_t> pt_ii, pt_jj;
   DevBuf d_pt;
   DevBuf d_jd;                 // proj_trans outputs inside dba_jdsa
+  DevBuf d_cov;                // L^-1 and S^-1 of dba_depth_cov
   int pt_M = 0, pt_N = 0;
   bool pt_contig = true;       // unique(ii) is a contiguous range of frames
   // NCCL
@@ -332,7 +333,7 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
 int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const float* disps_sens,
            const float* targets, const float* weights, const float* eta, const int64_t* ii_h, const int64_t* jj_h,
            int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
-           bool motion_only, float* dx_out, float* dz_out, cudaStream_t st) {
+           bool motion_only, float* dx_out, float* dz_out, cudaStream_t st, float* cov_out = nullptr) {
   g_launch_count = 0;
   int rc = prepare_plan(ctx, ii_h, jj_h, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only, st);
   if (rc) return rc;
@@ -385,6 +386,15 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");
     mark();
+    if (cov_out != nullptr) {
+      // depth covariance of THIS linearisation (chol.py:74-76): factor, then S^-1 and the per-pixel quadratic forms;
+      // the state is left untouched
+      if (ctx->coop_ctas <= 0) return fail_arg(ctx, "depth covariance needs the cooperative factorisation (system too large)");
+      CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st), "cholesky (cooperative)");
+      CK(ctx->d_cov.ensure(cov_scratch_floats(g.n6) * sizeof(float) + 16), "covariance scratch");
+      CK(launch_depth_cov(g, in, ws, ctx->d_cov.as<float>(), ctx->smem_cap, cov_out, st), "depth covariance");
+      break;
+    }
     if (ctx->opt_small && g.n6 <= cholesky_small_max_n())
       CK(launch_cholesky_small(ws, g.n6, st), "cholesky (single CTA)");
     else if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol)
@@ -397,6 +407,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     CK(launch_retract(g, in, ws, (it == iterations - 1) ? dx_out : nullptr, st), "retract");
     mark();
   }
+  if (cov_out != nullptr) { ctx->last_launches = g_launch_count; return 0; }
   if (prof && nev > 0) {
     CK(cudaEventSynchronize(ctx->ev[nev - 1]), "profile");
     for (int it = 0; it < iterations; ++it)
@@ -460,7 +471,7 @@ void dba_destroy(dba_ctx* c) {
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
-                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd};
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
@@ -514,6 +525,29 @@ int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, co
   }
   return run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ctx->h_idx, ctx->h_idx + E, E, N, ht,
                 wd, M, t0, t1, iterations, lm, ep, motion_only != 0, dx_out, dz_out, st);
+}
+
+int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* disps_sens,
+                  const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                  int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, float lm, float ep, float* dzcov_out,
+                  void* stream) {
+  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, 1, 0);
+  if (rc) return rc;
+  if (E <= 0 || !dzcov_out) return fail_arg(ctx, "depth covariance needs edges and an output buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  if (size_t(2 * E) > ctx->h_idx_cap) {
+    if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
+    ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
+    CK(cudaMallocHost(&ctx->h_idx, size_t(2 * E + 64) * sizeof(int64_t)), "pinned staging");
+    ctx->h_idx_cap = size_t(2 * E + 64);
+  }
+  CK(cudaMemcpyAsync(ctx->h_idx, ii, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "ii -> host");
+  CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
+  CK(cudaStreamSynchronize(st), "ii/jj -> host");
+  // the state is read-only on this path (run_ba's cov branch leaves before any retraction)
+  return run_ba(ctx, const_cast<float*>(poses), const_cast<float*>(disps), intrinsics, disps_sens, targets, weights, eta,
+                ctx->h_idx, ctx->h_idx + E, E, N, ht, wd, M, t0, t1, 1, lm, ep, false, nullptr, nullptr, st, dzcov_out);
 }
 
 int dba_ba_host(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,

@@ -1,0 +1,257 @@
+// Depth covariance of the Schur solve (hislam2/geom/chol.py:74-76, the third output of BA, geom/ba.py:98-107;
+// SURVEY.md section 8f rank 4):
+//     F = L^-1 (E Q) ; dzcov = colsum(F^2) + Q        with S = L L^T the damped reduced pose system
+// i.e. per pixel (k,p):  dzcov = Q^2 u^T S^-1 u + Q,  u = column (k,p) of E -- non-zero only in the 6-blocks of pose k
+// and of the poses k has edges to.  The reference forms F densely ([6P, M*HW]: 1.3 GB at 128 keyframes); here
+//   k_linv    W = L^-1 by 32-column blocks (one CTA per block column, forward substitution by blocks)
+//   k_wtw     S^-1 = W^T W (lower tiles, mirrored)
+//   k_dzcov   per (source keyframe, pixel tile): the columns of E are recomputed from the inputs (never stored),
+//             kept in shared memory, and the quadratic form runs over the (deg+1)^2 6x6 blocks of S^-1 it touches.
+#include "dba_kernels.h"
+#include "dba_math.cuh"
+
+namespace dba {
+
+namespace {
+
+constexpr int CB = 32;
+
+__device__ __forceinline__ float L_at(const float* __restrict__ L, int ld, int n, int r, int c) {
+  // the factor padded with an identity to a multiple of 32
+  return (r < n && c < n) ? __ldg(L + int64_t(r) * ld + c) : (r == c ? 1.f : 0.f);
+}
+
+// W [nkb*32, ldw] (zero-initialised): block column c of L^-1.
+__global__ void __launch_bounds__(256)
+k_linv(const float* __restrict__ L, int ld, int n, float* W, int ldw) {
+  __shared__ float sT[8][CB][CB + 1];
+  __shared__ float sX[CB][CB + 1];
+  const int nkb = (n + CB - 1) / CB;
+  const int c = blockIdx.x, c0 = c * CB;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int r = c; r < nkb; ++r) {
+    const int r0 = r * CB;
+    // T = sum_{m=c}^{r-1} L[r][m] W[m][c], the m range dealt over the warps; lane = column of the product
+    float acc[CB];
+#pragma unroll
+    for (int i = 0; i < CB; ++i) acc[i] = 0.f;
+    for (int m = c + warp; m < r; m += 8) {
+      const int m0 = m * CB;
+      float wk[CB];
+#pragma unroll
+      for (int k = 0; k < CB; ++k) wk[k] = __ldcg(W + int64_t(m0 + k) * ldw + c0 + lane);
+#pragma unroll 4
+      for (int i = 0; i < CB; ++i) {
+        float s = acc[i];
+#pragma unroll
+        for (int k = 0; k < CB; ++k) s = fmaf(L_at(L, ld, n, r0 + i, m0 + k), wk[k], s);
+        acc[i] = s;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < CB; ++i) sT[warp][i][lane] = acc[i];
+    __syncthreads();
+    for (int e = tid; e < CB * CB; e += 256) {
+      const int i = e >> 5, j = e & 31;
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) s += sT[w][i][j];
+      sX[i][j] = ((r == c && i == j) ? 1.f : 0.f) - s;       // right-hand side: delta - T
+    }
+    __syncthreads();
+    if (warp == 0) {                                          // W[r][c] = L_rr^-1 rhs, lane = column
+      float x[CB];
+#pragma unroll
+      for (int i = 0; i < CB; ++i) {
+        float s = sX[i][lane];
+#pragma unroll
+        for (int k = 0; k < CB; ++k)
+          if (k < i) s = fmaf(-L_at(L, ld, n, r0 + i, r0 + k), x[k], s);
+        x[i] = s / L_at(L, ld, n, r0 + i, r0 + i);
+      }
+#pragma unroll
+      for (int i = 0; i < CB; ++i) W[int64_t(r0 + i) * ldw + c0 + lane] = x[i];
+    }
+    __syncthreads();                                          // block-wide visibility of W[r][c] for the next steps
+  }
+}
+
+// Sinv = W^T W, lower tiles (a >= b) mirrored.  W is lower triangular by blocks: rows >= a only.
+__global__ void __launch_bounds__(256)
+k_wtw(const float* __restrict__ W, int ldw, int nkb, float* __restrict__ Sinv) {
+  __shared__ float sA[CB][CB + 1], sB[CB][CB + 1];
+  int a = int((sqrtf(8.0f * float(blockIdx.x) + 1.0f) - 1.0f) * 0.5f);
+  while ((a + 1) * (a + 2) / 2 <= int(blockIdx.x)) ++a;
+  while (a * (a + 1) / 2 > int(blockIdx.x)) --a;
+  const int b = int(blockIdx.x) - a * (a + 1) / 2;
+  const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;     // outputs (i = ty + 8q, j = tx)
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int r = a; r < nkb; ++r) {
+    for (int e = tid; e < CB * CB; e += 256) {
+      const int i = e >> 5, j = e & 31;
+      sA[i][j] = W[int64_t(r * CB + i) * ldw + a * CB + j];
+      sB[i][j] = W[int64_t(r * CB + i) * ldw + b * CB + j];
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < CB; ++k) {
+      const float bv = sB[k][tx];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[q] = fmaf(sA[k][ty + 8 * q], bv, acc[q]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int i = a * CB + ty + 8 * q, j = b * CB + tx;
+    Sinv[int64_t(i) * ldw + j] = acc[q];
+    Sinv[int64_t(j) * ldw + i] = acc[q];
+  }
+}
+
+constexpr int CV_CHUNK = 32;
+
+// one thread per pixel of (source keyframe slot m, PT-pixel tile); dynamic smem: u [(deg+1)*6][PT] | Sinv blocks
+__global__ void
+k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+        const float* __restrict__ targets, const float* __restrict__ weights, const int32_t* __restrict__ kx,
+        const int32_t* __restrict__ koff, const int32_t* __restrict__ cedge, const int32_t* __restrict__ cj, int HW, int wd,
+        int ntiles, int t0, int Pp, const float* __restrict__ Sinv, int lds, const float* __restrict__ Q,
+        float* __restrict__ dzcov) {
+  extern __shared__ float smem[];
+  __shared__ float sRt[CV_CHUNK * 12], sAd[CV_CHUNK * 36];
+  __shared__ int sedge[CV_CHUNK];
+  const int PT = blockDim.x;
+  const int m = blockIdx.x / ntiles, tile = blockIdx.x % ntiles;
+  const int tid = threadIdx.x;
+  const int k = kx[m];
+  const int e0 = koff[m], deg = koff[m + 1] - e0;
+  float* su = smem;                                         // [(1 + deg) * 6][PT]
+  float* sS = smem + size_t(1 + deg) * 6 * PT;              // [(1 + deg)][36]
+  int* sslot = reinterpret_cast<int*>(sS + size_t(1 + deg) * 36);
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int p = tile * PT + tid;
+  const bool inb = p < HW;
+  const float dd = inb ? disps[int64_t(k) * HW + p] : 0.f;
+  const int py = p / wd, px = p - py * wd;
+  const float xx = (float(px) - cx) / fx, yy = (float(py) - cy) / fy;
+  // entry 0 = pose k itself, entry 1 + e = the target pose of edge e; slot < 0: fixed pose, no row in S
+  for (int e = tid; e <= deg; e += PT) {
+    const int f = (e == 0) ? k : cj[e0 + e - 1];
+    const int s = f - t0;
+    sslot[e] = (s >= 0 && s < Pp) ? s : -1;
+  }
+  float ui[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int c0 = 0; c0 < deg; c0 += CV_CHUNK) {
+    const int nc = min(CV_CHUNK, deg - c0);
+    __syncthreads();
+    for (int le = tid; le < nc; le += PT) {
+      float Rt[12], Ad[36];
+      relative_pose_Rt(poses, k, cj[e0 + c0 + le], Rt);
+      adjoint_from_Rt(Rt, Ad);
+      for (int i = 0; i < 12; ++i) sRt[12 * le + i] = Rt[i];
+      for (int i = 0; i < 36; ++i) sAd[36 * le + i] = Ad[i];
+      sedge[le] = cedge[e0 + c0 + le];
+    }
+    __syncthreads();
+    for (int le = 0; le < nc; ++le) {
+      float Ej[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (inb) {
+        const float* wg = weights + int64_t(sedge[le]) * 2 * HW;
+        const float wx = __ldcs(wg + p), wy = __ldcs(wg + HW + p);
+        const Proj pr = project(sRt + 12 * le, xx, yy, dd, fx, fy, cx, cy);
+        // h = sum_rows w jz g (3-vector); Ej = [d h, X1 x h]   (Jj_r = [d g_r, X1 x g_r], dba_math.cuh)
+        const float s0 = kWeightScale * (pr.valid * wx) * pr.jz0, s1 = kWeightScale * (pr.valid * wy) * pr.jz1;
+        const float hx = s0 * pr.a0, hy = s1 * pr.b1, hz = s0 * pr.c0 + s1 * pr.c1;
+        Ej[0] = dd * hx; Ej[1] = dd * hy; Ej[2] = dd * hz;
+        Ej[3] = pr.X1.y * hz - pr.X1.z * hy;
+        Ej[4] = pr.X1.z * hx - pr.X1.x * hz;
+        Ej[5] = pr.X1.x * hy - pr.X1.y * hx;
+        const float* Ad = sAd + 36 * le;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          float s = 0.f;
+#pragma unroll
+          for (int t = 0; t < 6; ++t) s = fmaf(Ad[t * 6 + r], Ej[t], s);
+          ui[r] -= s;                                      // Ei = -Ad^T Ej (projective_ops.py:66)
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) su[(size_t(1 + c0 + le) * 6 + c) * PT + tid] = Ej[c];
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) su[size_t(c) * PT + tid] = ui[c];
+  __syncthreads();
+  float quad = 0.f;
+  for (int a = 0; a <= deg; ++a) {
+    const int sa = sslot[a];
+    if (sa < 0) continue;                                   // block-uniform
+    __syncthreads();
+    for (int e = tid; e < (a + 1) * 36; e += PT) {
+      const int b = e / 36, rc = e - b * 36, r = rc / 6, c = rc - r * 6;
+      const int sb = sslot[b];
+      sS[e] = (sb >= 0) ? Sinv[int64_t(6 * sa + r) * lds + 6 * sb + c] : 0.f;
+    }
+    __syncthreads();
+    float ua[6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) ua[c] = su[(size_t(a) * 6 + c) * PT + tid];
+    for (int b = 0; b <= a; ++b) {
+      const float* Sb = sS + b * 36;
+      float ub[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) ub[c] = su[(size_t(b) * 6 + c) * PT + tid];
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s = fmaf(Sb[r * 6 + c], ub[c], s);
+        t = fmaf(ua[r], s, t);
+      }
+      quad += (b == a) ? t : 2.f * t;
+    }
+  }
+  if (inb) {
+    const float q = Q[int64_t(m) * HW + p];
+    dzcov[int64_t(m) * HW + p] = q * q * quad + q;
+  }
+}
+
+}  // namespace
+
+size_t cov_scratch_floats(int n) {
+  const size_t npad = size_t((n + CB - 1) / CB) * CB;
+  return 2 * npad * npad;
+}
+
+cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* scratch,
+                             size_t smem_cap, float* dzcov, cudaStream_t st) {
+  const int n = g.n6;
+  const int nkb = (n + CB - 1) / CB, npad = nkb * CB;
+  float* W = scratch;
+  float* Sinv = scratch + size_t(npad) * npad;
+  cudaError_t err = cudaMemsetAsync(W, 0, size_t(npad) * npad * sizeof(float), st);
+  if (err != cudaSuccess) return err;
+  if (n > 0) {
+    k_linv<<<nkb, 256, 0, st>>>(ws.Lm, ws.ldA, n, W, npad);
+    k_wtw<<<nkb * (nkb + 1) / 2, 256, 0, st>>>(W, npad, nkb, Sinv);
+    g_launch_count += 2;
+  }
+  if (g.M > 0) {
+    int PT = 128;
+    auto bytes = [&](int pt) { return (size_t(1 + g.degmax) * 6 * pt + size_t(1 + g.degmax) * 37 + 8) * sizeof(float); };
+    while (PT > 32 && bytes(PT) > (smem_cap > 12288 ? smem_cap - 12288 : 0)) PT >>= 1;
+    if (bytes(PT) + 12288 > smem_cap) return cudaErrorInvalidConfiguration;
+    err = cudaFuncSetAttribute(k_dzcov, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes(PT)));
+    if (err != cudaSuccess) return err;
+    const int ntiles = (g.HW + PT - 1) / PT;
+    k_dzcov<<<g.M * ntiles, PT, bytes(PT), st>>>(in.poses, in.disps, in.intrinsics, in.targets, in.weights, g.kx, g.koff,
+                                                  g.cedge, g.cj, g.HW, g.wd, ntiles, g.t0, g.Pp, Sinv, npad, ws.Q, dzcov);
+    g_launch_count++;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace dba

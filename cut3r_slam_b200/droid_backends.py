@@ -145,6 +145,23 @@ def ba(*args):
     return [dx, dz]
 
 
+def depth_cov(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, lm, ep):
+    """The depth covariance the reference's torch BA returns as its third output (hislam2/geom/ba.py:98-107,
+    chol.py:74-76), at the given state and with the argument list of `ba` (no iterations / motion_only):
+    dzcov [M,ht,wd], rows in sorted(unique(ii)) order.  poses and disps are not modified."""
+    N, ht, wd, E, M = _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, False, True)
+    ctx = context(poses.device)
+    cov = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+    sens = disps_sens if (disps_sens is not None and disps_sens.numel() > 0) else None
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        rc = ctx.lib.dba_depth_cov(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(sens), _ptr(targets),
+                                   _ptr(weights), _ptr(eta), _ptr(ii), _ptr(jj), E, N, ht, wd, M, int(t0), int(t1),
+                                   float(lm), float(ep), _ptr(cov), C.c_void_p(stream))
+    ctx.check(rc)
+    return cov
+
+
 def ba_host(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
             motion_only, device=None):
     """Same op on HOST tensors (pinned for full copy speed): copies in, runs, copies poses/disps back.

@@ -99,6 +99,15 @@ int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrin
              const int64_t* jj, int64_t E, int64_t N, int ht, int wd, int hs, int ws, int64_t M, float alpha, float ep,
              float lm, float* dzcov_out, void* stream);
 
+/* ---- depth covariance of the Schur solve: the third output of BA (hislam2/geom/ba.py:98-107, chol.py:74-76;
+ * SURVEY.md 8f rank 4).  Linearises at the GIVEN state exactly as one `ba` iteration would (same arguments, same
+ * damping lm / ep), factors the reduced pose system and writes dzcov [M,ht,wd] = diag(E^T S^-1 E) Q^2 + Q, rows in
+ * sorted(unique(ii)) order.  poses / disps are not modified. */
+int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* disps_sens,
+                  const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                  int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, float lm, float ep, float* dzcov_out,
+                  void* stream);
+
 /* ---- the elementwise steps either side of `ba` in FactorGraph.update
  * reproject(ii, jj) -> (coords, valid)  [hislam2/depth_video.pyc reproject@170-178 = projective_transform,
  *   hislam2/geom/projective_ops.py:44-74 with jacobian=False]: coords [E,ht,wd,2] = pixel of frame jj[e] that pixel

@@ -300,6 +300,22 @@ def oracle_ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, j
     return new_poses, new_disps
 
 
+def depth_cov(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, lm, ep,
+              dtype=torch.float64):
+    """The third output of the reference's BA (ba.py:98,107 <- chol.py:74-76) at the given state, through the
+    `droid_backends.ba` argument list: dzcov [M,ht*wd], rows in sorted(unique(ii)) order."""
+    p = poses[:t1].to(dtype)
+    d = disps[:t1].to(dtype)
+    tgt = targets.permute(0, 2, 3, 1).to(dtype).contiguous()
+    wgt = weights.permute(0, 2, 3, 1).to(dtype).contiguous()
+    ds = None
+    if disps_sens is not None and bool((disps_sens[:t1] > 0).any()):
+        ds = disps_sens[:t1].to(dtype)
+    lin = linearize(tgt, wgt, eta.to(dtype), p, d, intrinsics.to(dtype), ii.long().cpu(), jj.long().cpu(), t0, ds)
+    sol = schur_solve(lin["H"], lin["E"], lin["C"], lin["v"], lin["w"], ep=ep, lm=lm, with_dzcov=True)
+    return sol["dzcov"]
+
+
 # --------------------------------------------------------------------------------------------
 # companion ops -- PARITY UNPINNED (CUDA source absent; definitions documented in DESIGN.md)
 # --------------------------------------------------------------------------------------------
