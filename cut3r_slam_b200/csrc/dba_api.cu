@@ -707,6 +707,7 @@ int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrin
   if (!ctx) return -1;
   if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || hs <= 0 || ws <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
   if (hs * ws > jdsa_max_nodes()) return fail_arg(ctx, "scale grid larger than 64 nodes per keyframe");
+  if (jdsa_dynamic_smem(ht, wd) > ctx->smem_cap) return fail_arg(ctx, "ht*wd too large for the JDSA kernel's shared-memory maps");
   if (E == 0) return M == 0 ? 0 : fail_arg(ctx, "M must be |unique(ii)|");
   if (!poses || !disps || !intrinsics || !disps_prior || !dscales || !targets || !weights || !eta || !ii || !jj || !dzcov_out)
     return fail_arg(ctx, "NULL argument");

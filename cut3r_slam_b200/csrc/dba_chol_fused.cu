@@ -666,6 +666,7 @@ cudaError_t launch_cholesky_small(const Workspace& ws, int n, cudaStream_t st) {
 }
 
 size_t cholesky_ldiag_floats(int n) { return size_t((n + NB - 1) / NB) * LD_STRIDE; }
+void cholesky_ldiag_layout(int* stride, int* linv_offset) { *stride = LD_STRIDE; *linv_offset = LD_LINV; }
 
 int cholesky_coop_max_ctas(int n) {
   int dev = 0, sms = 0, per = 0, coop = 0;

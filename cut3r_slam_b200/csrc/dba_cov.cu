@@ -21,16 +21,23 @@ __device__ __forceinline__ float L_at(const float* __restrict__ L, int ld, int n
   return (r < n && c < n) ? __ldg(L + int64_t(r) * ld + c) : (r == c ? 1.f : 0.f);
 }
 
-// W [nkb*32, ldw] (zero-initialised): block column c of L^-1.
+// W [nkb*32, ldw] (zero-initialised): block column c of L^-1 by block forward substitution,
+//   W[c][c] = L_cc^-1 ;  W[r][c] = -L_rr^-1 sum_{m=c}^{r-1} L[r][m] W[m][c]
+// with the inverses of the diagonal blocks taken from the factorisation (Ldiag, identity-padded like L_at).
 __global__ void __launch_bounds__(256)
-k_linv(const float* __restrict__ L, int ld, int n, float* W, int ldw) {
-  __shared__ float sT[8][CB][CB + 1];
-  __shared__ float sX[CB][CB + 1];
+k_linv(const float* __restrict__ L, int ld, int n, const float* __restrict__ Ldiag, int ld_stride, int ld_linv, float* W,
+       int ldw) {
+  __shared__ __align__(16) float sT[8][CB][CB + 4];         // rows 16-byte aligned: broadcast reads as float4
+  __shared__ float sX[CB][CB + 1], sLi[CB][CB + 1];
   const int nkb = (n + CB - 1) / CB;
   const int c = blockIdx.x, c0 = c * CB;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int r = c; r < nkb; ++r) {
+  for (int e = tid; e < CB * CB; e += 256)
+    W[int64_t(c0 + (e >> 5)) * ldw + c0 + (e & 31)] = __ldg(Ldiag + int64_t(c) * ld_stride + ld_linv + e);
+  __syncthreads();
+  for (int r = c + 1; r < nkb; ++r) {
     const int r0 = r * CB;
+    for (int e = tid; e < CB * CB; e += 256) sLi[e >> 5][e & 31] = __ldg(Ldiag + int64_t(r) * ld_stride + ld_linv + e);
     // T = sum_{m=c}^{r-1} L[r][m] W[m][c], the m range dealt over the warps; lane = column of the product
     float acc[CB];
 #pragma unroll
@@ -40,14 +47,26 @@ k_linv(const float* __restrict__ L, int ld, int n, float* W, int ldw) {
       float wk[CB];
 #pragma unroll
       for (int k = 0; k < CB; ++k) wk[k] = __ldcg(W + int64_t(m0 + k) * ldw + c0 + lane);
-#pragma unroll 4
-      for (int i = 0; i < CB; ++i) {
-        float s = acc[i];
+      // the L block goes through this warp's slice of sT (free until the partial sums are parked there)
+      __syncwarp();
 #pragma unroll
-        for (int k = 0; k < CB; ++k) s = fmaf(L_at(L, ld, n, r0 + i, m0 + k), wk[k], s);
-        acc[i] = s;
+      for (int i = 0; i < CB; ++i) sT[warp][i][lane] = L_at(L, ld, n, r0 + i, m0 + lane);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < CB; ++i) {
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < CB; k += 4) {
+          const float4 l4 = *reinterpret_cast<const float4*>(&sT[warp][i][k]);
+          s0 = fmaf(l4.x, wk[k], s0);
+          s1 = fmaf(l4.y, wk[k + 1], s1);
+          s0 = fmaf(l4.z, wk[k + 2], s0);
+          s1 = fmaf(l4.w, wk[k + 3], s1);
+        }
+        acc[i] += s0 + s1;
       }
     }
+    __syncwarp();
 #pragma unroll
     for (int i = 0; i < CB; ++i) sT[warp][i][lane] = acc[i];
     __syncthreads();
@@ -56,21 +75,15 @@ k_linv(const float* __restrict__ L, int ld, int n, float* W, int ldw) {
       float s = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) s += sT[w][i][j];
-      sX[i][j] = ((r == c && i == j) ? 1.f : 0.f) - s;       // right-hand side: delta - T
+      sX[i][j] = s;
     }
     __syncthreads();
-    if (warp == 0) {                                          // W[r][c] = L_rr^-1 rhs, lane = column
-      float x[CB];
+    for (int e = tid; e < CB * CB; e += 256) {                 // W[r][c] = -L_rr^-1 T
+      const int i = e >> 5, j = e & 31;
+      float s = 0.f;
 #pragma unroll
-      for (int i = 0; i < CB; ++i) {
-        float s = sX[i][lane];
-#pragma unroll
-        for (int k = 0; k < CB; ++k)
-          if (k < i) s = fmaf(-L_at(L, ld, n, r0 + i, r0 + k), x[k], s);
-        x[i] = s / L_at(L, ld, n, r0 + i, r0 + i);
-      }
-#pragma unroll
-      for (int i = 0; i < CB; ++i) W[int64_t(r0 + i) * ldw + c0 + lane] = x[i];
+      for (int k = 0; k < CB; ++k) s = fmaf(sLi[i][k], sX[k][j], s);
+      W[int64_t(r0 + i) * ldw + c0 + j] = -s;
     }
     __syncthreads();                                          // block-wide visibility of W[r][c] for the next steps
   }
@@ -128,7 +141,7 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
   const int e0 = koff[m], deg = koff[m + 1] - e0;
   float* su = smem;                                         // [(1 + deg) * 6][PT]
   float* sS = smem + size_t(1 + deg) * 6 * PT;              // [(1 + deg)][36]
-  int* sslot = reinterpret_cast<int*>(sS + size_t(1 + deg) * 36);
+  int* sslot = reinterpret_cast<int*>(sS + size_t(1 + deg) * 72);
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
   const int p = tile * PT + tid;
   const bool inb = p < HW;
@@ -154,11 +167,19 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
       sedge[le] = cedge[e0 + c0 + le];
     }
     __syncthreads();
+    float nwx = 0.f, nwy = 0.f;                             // weights of the next edge, one edge ahead
+    if (inb && nc > 0) {
+      const float* wg = weights + int64_t(sedge[0]) * 2 * HW;
+      nwx = __ldcs(wg + p); nwy = __ldcs(wg + HW + p);
+    }
     for (int le = 0; le < nc; ++le) {
       float Ej[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const float wx = nwx, wy = nwy;
+      if (inb && le + 1 < nc) {
+        const float* wg = weights + int64_t(sedge[le + 1]) * 2 * HW;
+        nwx = __ldcs(wg + p); nwy = __ldcs(wg + HW + p);
+      }
       if (inb) {
-        const float* wg = weights + int64_t(sedge[le]) * 2 * HW;
-        const float wx = __ldcs(wg + p), wy = __ldcs(wg + HW + p);
         const Proj pr = project(sRt + 12 * le, xx, yy, dd, fx, fy, cx, cy);
         // h = sum_rows w jz g (3-vector); Ej = [d h, X1 x h]   (Jj_r = [d g_r, X1 x g_r], dba_math.cuh)
         const float s0 = kWeightScale * (pr.valid * wx) * pr.jz0, s1 = kWeightScale * (pr.valid * wy) * pr.jz1;
@@ -184,34 +205,51 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
   for (int c = 0; c < 6; ++c) su[size_t(c) * PT + tid] = ui[c];
   __syncthreads();
   float quad = 0.f;
-  for (int a = 0; a <= deg; ++a) {
+  // rows of S^-1 blocks for entry a: [b <= a][6][6], double-buffered -- the next row is in flight while this one is used
+  const int rowlen = (1 + deg) * 36;
+  float* sSb[2] = {sS, sS + rowlen};
+  auto fetch = [&](int a, float* dst) {                     // cp.async: global -> shared without registers
     const int sa = sslot[a];
-    if (sa < 0) continue;                                   // block-uniform
-    __syncthreads();
+    if (sa < 0) return;
     for (int e = tid; e < (a + 1) * 36; e += PT) {
       const int b = e / 36, rc = e - b * 36, r = rc / 6, c = rc - r * 6;
       const int sb = sslot[b];
-      sS[e] = (sb >= 0) ? Sinv[int64_t(6 * sa + r) * lds + 6 * sb + c] : 0.f;
+      const float* src = (sb >= 0) ? Sinv + int64_t(6 * sa + r) * lds + 6 * sb + c : Sinv;
+      const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(dst + e));
+      const int sz = (sb >= 0) ? 4 : 0;                     // src-size 0: zero fill
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
     }
-    __syncthreads();
+  };
+  fetch(0, sSb[0]);
+  for (int a = 0; a <= deg; ++a) {
+    float* cur = sSb[a & 1];
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+    __syncthreads();                                        // row a landed; everyone is done with the other buffer
+    if (a + 1 <= deg) fetch(a + 1, sSb[(a + 1) & 1]);
+    if (sslot[a] < 0) continue;                             // block-uniform: a fixed pose has no row in S
     float ua[6];
 #pragma unroll
     for (int c = 0; c < 6; ++c) ua[c] = su[(size_t(a) * 6 + c) * PT + tid];
+    // t = sum_{b<a} S_ab u_b + S_aa u_a / 2 ; quad += 2 u_a . t   (S symmetric: each off-diagonal pair once)
+    float t[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int b = 0; b <= a; ++b) {
-      const float* Sb = sS + b * 36;
+      const float4* Sb = reinterpret_cast<const float4*>(cur + b * 36);
+      float S[36];
+#pragma unroll
+      for (int q = 0; q < 9; ++q) { const float4 v = Sb[q]; S[4 * q] = v.x; S[4 * q + 1] = v.y; S[4 * q + 2] = v.z; S[4 * q + 3] = v.w; }
+      const float sc = (b == a) ? 0.5f : 1.0f;
       float ub[6];
 #pragma unroll
-      for (int c = 0; c < 6; ++c) ub[c] = su[(size_t(b) * 6 + c) * PT + tid];
-      float t = 0.f;
+      for (int c = 0; c < 6; ++c) ub[c] = sc * su[(size_t(b) * 6 + c) * PT + tid];
 #pragma unroll
-      for (int r = 0; r < 6; ++r) {
-        float s = 0.f;
+      for (int r = 0; r < 6; ++r)
 #pragma unroll
-        for (int c = 0; c < 6; ++c) s = fmaf(Sb[r * 6 + c], ub[c], s);
-        t = fmaf(ua[r], s, t);
-      }
-      quad += (b == a) ? t : 2.f * t;
+        for (int c = 0; c < 6; ++c) t[r] = fmaf(S[r * 6 + c], ub[c], t[r]);
     }
+    float dq = 0.f;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) dq = fmaf(ua[r], t[r], dq);
+    quad = fmaf(2.f, dq, quad);
   }
   if (inb) {
     const float q = Q[int64_t(m) * HW + p];
@@ -235,13 +273,15 @@ cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Wor
   cudaError_t err = cudaMemsetAsync(W, 0, size_t(npad) * npad * sizeof(float), st);
   if (err != cudaSuccess) return err;
   if (n > 0) {
-    k_linv<<<nkb, 256, 0, st>>>(ws.Lm, ws.ldA, n, W, npad);
+    int ld_stride = 0, ld_linv = 0;
+    cholesky_ldiag_layout(&ld_stride, &ld_linv);
+    k_linv<<<nkb, 256, 0, st>>>(ws.Lm, ws.ldA, n, ws.Ldiag, ld_stride, ld_linv, W, npad);
     k_wtw<<<nkb * (nkb + 1) / 2, 256, 0, st>>>(W, npad, nkb, Sinv);
     g_launch_count += 2;
   }
   if (g.M > 0) {
     int PT = 128;
-    auto bytes = [&](int pt) { return (size_t(1 + g.degmax) * 6 * pt + size_t(1 + g.degmax) * 37 + 8) * sizeof(float); };
+    auto bytes = [&](int pt) { return (size_t(1 + g.degmax) * 6 * pt + size_t(1 + g.degmax) * 73 + 8) * sizeof(float); };
     while (PT > 32 && bytes(PT) > (smem_cap > 12288 ? smem_cap - 12288 : 0)) PT >>= 1;
     if (bytes(PT) + 12288 > smem_cap) return cudaErrorInvalidConfiguration;
     err = cudaFuncSetAttribute(k_dzcov, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes(PT)));

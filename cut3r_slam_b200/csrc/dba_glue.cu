@@ -16,6 +16,7 @@ namespace {
 
 constexpr int RP_T = 256;
 
+// grid (nsplit, E): one relative pose per CTA, the CTA strides over its share of the pixels
 __global__ void __launch_bounds__(RP_T)
 k_reproject(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
             const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int HW, int wd, float2* __restrict__ coords,
@@ -25,82 +26,134 @@ k_reproject(const float* __restrict__ poses, const float* __restrict__ disps, co
   const int i = int(ii[e]), j = int(jj[e]);
   if (threadIdx.x == 0) relative_pose_Rt(poses, i, j, sRt);
   __syncthreads();
-  const int p = blockIdx.x * RP_T + threadIdx.x;
-  if (p >= HW) return;
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
-  const int py = p / wd, px = p - py * wd;
-  const float d = disps[int64_t(i) * HW + p];
-  const Proj pr = project(sRt, (float(px) - cx) / fx, (float(py) - cy) / fy, d, fx, fy, cx, cy);
-  __stcs(coords + int64_t(e) * HW + p, make_float2(pr.u, pr.v));
-  __stcs(valid + int64_t(e) * HW + p, pr.valid);
+  const float* dsrc = disps + int64_t(i) * HW;
+  for (int p = blockIdx.x * RP_T + threadIdx.x; p < HW; p += gridDim.x * RP_T) {
+    const int py = p / wd, px = p - py * wd;
+    const Proj pr = project(sRt, (float(px) - cx) / fx, (float(py) - cy) / fy, __ldg(dsrc + p), fx, fy, cx, cy);
+    __stcs(coords + int64_t(e) * HW + p, make_float2(pr.u, pr.v));
+    __stcs(valid + int64_t(e) * HW + p, pr.valid);
+  }
 }
 
 constexpr int UP_T = 256;          // 8 sub-columns j x 32 coarse pixels
-constexpr int UP_C = 4;            // channels per pass
 
-__global__ void __launch_bounds__(UP_T)
-k_cvx_upsample(const float* __restrict__ data, const float* __restrict__ mask, int ht, int wd, int dim,
+// NC channels per pass (1, 2 or 4); channels [c0, c0 + nc) of `dim`
+template <int NC>
+__global__ void __launch_bounds__(UP_T, 3)
+k_cvx_upsample(const float* __restrict__ data, const float* __restrict__ mask, int ht, int wd, int dim, int c0, int nc,
                float* __restrict__ up) {
-  __shared__ float srow[8][32 * 8 * UP_C];
+  __shared__ float srow[8][32 * 8 * NC + 4];
   const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * 32;
   const int tid = threadIdx.x, j = tid >> 5, xx = tid & 31, x = x0 + xx;
   const int nx = min(32, wd - x0);
   const bool act = xx < nx;
   const int64_t plane = int64_t(ht) * wd;
-  bool inside[9];
+  unsigned inside = 0;
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
     const int yy = y + k / 3 - 1, xk = x + k % 3 - 1;
-    inside[k] = act && yy >= 0 && yy < ht && xk >= 0 && xk < wd;
+    if (act && yy >= 0 && yy < ht && xk >= 0 && xk < wd) inside |= 1u << k;
   }
-  for (int c0 = 0; c0 < dim; c0 += UP_C) {
-    const int nc = min(UP_C, dim - c0);
-    float nb[9][UP_C];
+  float nb[9][NC];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const int yy = y + k / 3 - 1, xk = x + k % 3 - 1;
+#pragma unroll
+    for (int c = 0; c < NC; ++c)
+      nb[k][c] = ((inside >> k & 1u) && c < nc) ? __ldg(data + ((int64_t(b) * ht + yy) * wd + xk) * dim + c0 + c) : 0.f;
+  }
+  // mask viewed as [B,9,8,8,ht,wd] (droid_net.py:24): element (b,k,i,j,y,x)
+  const float* mb = mask + (int64_t(b) * 9 * 64 + j) * plane + int64_t(y) * wd + x;
+#pragma unroll 2
+  for (int i = 0; i < 8; ++i) {
+    float l[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+      l[k] = (inside >> k & 1u) ? __ldcs(mb + int64_t((k * 8 + i) * 8) * plane) : -INFINITY;
+    float mx = l[4];                                     // the centre is always inside
+#pragma unroll
+    for (int k = 0; k < 9; ++k) mx = fmaxf(mx, l[k]);
+    float den = 0.f, acc[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) acc[c] = 0.f;
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
-      const int yy = y + k / 3 - 1, xk = x + k % 3 - 1;
+      // ex2.approx of a non-positive argument: relative error <= 3e-6 on terms that are themselves <= 1 (the largest
+      // term is exactly 1), i.e. <= 3e-7 of the convex combination -- inside the 2e-6 parity tolerance
+      const float ev = (inside >> k & 1u) ? __expf(l[k] - mx) : 0.f;
+      den += ev;
 #pragma unroll
-      for (int c = 0; c < UP_C; ++c)
-        nb[k][c] = (inside[k] && c < nc) ? data[((int64_t(b) * ht + yy) * wd + xk) * dim + c0 + c] : 0.f;
+      for (int c = 0; c < NC; ++c) acc[c] = fmaf(ev, nb[k][c], acc[c]);
     }
-#pragma unroll 2
-    for (int i = 0; i < 8; ++i) {
-      float l[9];
+    const float inv = 1.0f / den;
+    if (act) {
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (c < nc) srow[i][(xx * 8 + j) * nc + c] = acc[c] * inv;
+    }
+  }
+  __syncthreads();
+  // fine rows 8y .. 8y+7, columns 8x0 .. 8x0 + 8nx - 1: contiguous runs when one pass covers all channels
+  const int run = nx * 8 * nc;
+  for (int i = 0; i < 8; ++i) {
+    float* dst = up + ((int64_t(b) * 8 * ht + 8 * y + i) * 8 * wd + 8 * x0) * dim;
+    for (int t = tid; t < run; t += UP_T) {
+      const int col = t / nc, c = t - col * nc;
+      __stcs(dst + int64_t(col) * dim + c0 + c, srow[i][t]);
+    }
+  }
+}
+
+// dim == 1 (disparities, the case FactorGraph.update runs): one thread per coarse pixel of the FLATTENED image, so
+// that a CTA reads one contiguous 1 KB run from each of the 576 logit planes (no partially filled tiles at the row
+// ends) with 36 independent loads in flight per thread, and writes each fine row as 16-byte pieces that
+// interleave to contiguous runs across the warp -- no shared memory, no barriers.
+__global__ void __launch_bounds__(256, 3)
+k_cvx_upsample_flat(const float* __restrict__ data, const float* __restrict__ mask, int ht, int wd,
+                    float* __restrict__ up) {
+  const int b = blockIdx.y;
+  const int plane = ht * wd;
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  if (p >= plane) return;
+  const int y = p / wd, x = p - y * wd;
+  unsigned inside = 0;
+  float nb[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const int yy = y + k / 3 - 1, xk = x + k % 3 - 1;
+    const bool in = yy >= 0 && yy < ht && xk >= 0 && xk < wd;
+    if (in) inside |= 1u << k;
+    nb[k] = in ? __ldg(data + (int64_t(b) * ht + yy) * wd + xk) : 0.f;
+  }
+  const float* mb = mask + int64_t(b) * 576 * plane + p;           // element (b,k,i,j,y,x) of [B,9,8,8,ht,wd]
+  float* ub = up + (int64_t(b) * 8 * ht + 8 * y) * 8 * wd + 8 * x;
+#pragma unroll 1
+  for (int ih = 0; ih < 16; ++ih) {                        // (fine row i, half of its 8 sub-columns)
+    const int i = ih >> 1, j0 = (ih & 1) * 4;
+    float l[9][4];
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        l[k][j] = (inside >> k & 1u) ? __ldcs(mb + int64_t((k * 8 + i) * 8 + j0 + j) * plane) : -INFINITY;
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float mx = l[4][j];                                 // the centre is always inside
+#pragma unroll
+      for (int k = 0; k < 9; ++k) mx = fmaxf(mx, l[k][j]);
+      float den = 0.f, acc = 0.f;
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
-        // mask viewed as [B,9,8,8,ht,wd] (droid_net.py:24)
-        const int64_t off = (((int64_t(b) * 9 + k) * 8 + i) * 8 + j) * plane + int64_t(y) * wd + x;
-        l[k] = inside[k] ? __ldcs(mask + off) : -INFINITY;
-      }
-      float mx = l[4];                                     // the centre is always inside
-#pragma unroll
-      for (int k = 0; k < 9; ++k) mx = fmaxf(mx, l[k]);
-      float den = 0.f, acc[UP_C] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        const float ev = inside[k] ? expf(l[k] - mx) : 0.f;
+        const float ev = (inside >> k & 1u) ? __expf(l[k][j] - mx) : 0.f;   // see k_cvx_upsample on the accuracy
         den += ev;
-#pragma unroll
-        for (int c = 0; c < UP_C; ++c) acc[c] = fmaf(ev, nb[k][c], acc[c]);
+        acc = fmaf(ev, nb[k], acc);
       }
-      const float inv = 1.0f / den;
-      if (act) {
-#pragma unroll
-        for (int c = 0; c < UP_C; ++c)
-          if (c < nc) srow[i][(xx * 8 + j) * nc + c] = acc[c] * inv;
-      }
+      o[j] = acc / den;
     }
-    __syncthreads();
-    // fine rows 8y .. 8y+7, columns 8x0 .. 8x0 + 8nx - 1: contiguous runs when one pass covers all channels
-    const int run = nx * 8 * nc;
-    for (int i = 0; i < 8; ++i) {
-      float* dst = up + ((int64_t(b) * 8 * ht + 8 * y + i) * 8 * wd + 8 * x0) * dim;
-      for (int t = tid; t < run; t += UP_T) {
-        const int col = t / nc, c = t - col * nc;
-        __stcs(dst + int64_t(col) * dim + c0 + c, srow[i][t]);
-      }
-    }
-    __syncthreads();
+    // 8x + j0 floats into fine row 8y + i: 16-byte aligned; the warp's pieces of a row are contiguous
+    __stcs(reinterpret_cast<float4*>(ub + int64_t(i) * 8 * wd + j0), make_float4(o[0], o[1], o[2], o[3]));
   }
 }
 
@@ -109,7 +162,12 @@ k_cvx_upsample(const float* __restrict__ data, const float* __restrict__ mask, i
 cudaError_t launch_reproject(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                              const int64_t* jj, int E, int HW, int wd, float* coords, float* valid, cudaStream_t st) {
   if (E <= 0) return cudaSuccess;
-  dim3 grid((HW + RP_T - 1) / RP_T, E);
+  // about 16 CTAs per SM in total; an edge is never split finer than one pixel per thread
+  int nsplit = (148 * 16 + E - 1) / E;
+  const int maxsplit = (HW + RP_T - 1) / RP_T;
+  if (nsplit > maxsplit) nsplit = maxsplit;
+  if (nsplit < 1) nsplit = 1;
+  dim3 grid(nsplit, E);
   k_reproject<<<grid, RP_T, 0, st>>>(poses, disps, intr, ii, jj, HW, wd, reinterpret_cast<float2*>(coords), valid);
   g_launch_count++;
   return cudaGetLastError();
@@ -118,9 +176,20 @@ cudaError_t launch_reproject(const float* poses, const float* disps, const float
 cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int ht, int wd, int dim, float* up,
                                 cudaStream_t st) {
   if (B <= 0) return cudaSuccess;
+  if (dim == 1 && (reinterpret_cast<uintptr_t>(up) & 15u) == 0) {
+    dim3 gridf((ht * wd + 255) / 256, B);
+    k_cvx_upsample_flat<<<gridf, 256, 0, st>>>(data, mask, ht, wd, up);
+    g_launch_count++;
+    return cudaGetLastError();
+  }
   dim3 grid((wd + 31) / 32, ht, B);
-  k_cvx_upsample<<<grid, UP_T, 0, st>>>(data, mask, ht, wd, dim, up);
-  g_launch_count++;
+  for (int c0 = 0; c0 < dim; c0 += 4) {
+    const int nc = dim - c0 < 4 ? dim - c0 : 4;
+    if (nc == 1) k_cvx_upsample<1><<<grid, UP_T, 0, st>>>(data, mask, ht, wd, dim, c0, nc, up);
+    else if (nc == 2) k_cvx_upsample<2><<<grid, UP_T, 0, st>>>(data, mask, ht, wd, dim, c0, nc, up);
+    else k_cvx_upsample<4><<<grid, UP_T, 0, st>>>(data, mask, ht, wd, dim, c0, nc, up);
+    g_launch_count++;
+  }
   return cudaGetLastError();
 }
 

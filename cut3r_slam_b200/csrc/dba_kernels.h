@@ -103,10 +103,12 @@ cudaError_t launch_reproject(const float* poses, const float* disps, const float
                              const int64_t* jj, int E, int HW, int wd, float* coords, float* valid, cudaStream_t st);
 cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int ht, int wd, int dim, float* up,
                                 cudaStream_t st);
+void cholesky_ldiag_layout(int* stride, int* linv_offset);   // per 32-block: where L_kk^-1 (row-major 32x32) sits
 size_t cov_scratch_floats(int n);
 cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* scratch,
                              size_t smem_cap, float* dzcov, cudaStream_t st);
 int jdsa_max_nodes();
+size_t jdsa_dynamic_smem(int ht, int wd);
 cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,
                         float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,
                         float ep, float lm, float* dzcov, float* dz_out, float* dso_out, cudaStream_t st);

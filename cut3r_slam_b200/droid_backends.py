@@ -238,6 +238,26 @@ def depth_filter(poses, disps, intrinsics, ix, thresh):
     return out
 
 
+_sources_cache = {}
+
+
+def _num_sources(ii):
+    """|unique(ii)| without a sort + synchronisation on every call: remembered per (storage, version, length) of the
+    edge list.  A stale hit (storage reused by another tensor) cannot pass silently: the library counts the source
+    keyframes itself and rejects a wrong M, and the callers below then recount."""
+    key = (ii.data_ptr(), ii._version, ii.numel(), ii.device.index)
+    M = _sources_cache.get(key)
+    if M is None:
+        if len(_sources_cache) > 64:
+            _sources_cache.clear()
+        M = _sources_cache[key] = int(torch.unique(ii).numel())
+    return M
+
+
+def _forget_sources(ii):
+    _sources_cache.pop((ii.data_ptr(), ii._version, ii.numel(), ii.device.index), None)
+
+
 def proj_trans(poses, disps, intrinsics, targets, weights, ii, jj):
     """droid_backends.proj_trans(poses, disps, intrinsics, target, weight, ii, jj) -> (C, w)
     (hislam2/geom/ba.py:200).  C, w [M,ht,wd] with M = |unique(ii)|, rows in sorted(unique(ii)) order."""
@@ -255,15 +275,20 @@ def proj_trans(poses, disps, intrinsics, targets, weights, ii, jj):
     for t, nm in ((targets, "targets"), (weights, "weights")):
         if tuple(t.shape) != (E, 2, ht, wd):
             raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
-    M = int(torch.unique(ii).numel())
-    Cm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
-    wm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
     ctx = context(poses.device)
-    with torch.cuda.device(poses.device):
-        stream = torch.cuda.current_stream(poses.device).cuda_stream
-        ctx.check(ctx.lib.dba_proj_trans(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(targets),
-                                         _ptr(weights), _ptr(ii), _ptr(jj), E, N, ht, wd, M, _ptr(Cm), _ptr(wm),
-                                         C.c_void_p(stream)))
+    for attempt in (0, 1):
+        M = _num_sources(ii)
+        Cm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+        wm = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
+        with torch.cuda.device(poses.device):
+            stream = torch.cuda.current_stream(poses.device).cuda_stream
+            rc = ctx.lib.dba_proj_trans(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(targets),
+                                        _ptr(weights), _ptr(ii), _ptr(jj), E, N, ht, wd, M, _ptr(Cm), _ptr(wm),
+                                        C.c_void_p(stream))
+        if rc == 0 or attempt == 1:
+            break
+        _forget_sources(ii)                                # possibly a stale count: recount once
+    ctx.check(rc)
     return Cm, wm
 
 
@@ -313,7 +338,10 @@ def JDSA(target, weight, eta, poses, disps, intrinsics, disps_prior, dscales, ii
     for t, nm in ((target, "target"), (weight, "weight")):
         if tuple(t.shape) != (E, 2, ht, wd):
             raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
-    M = int(torch.unique(ii).numel())
+    M = _num_sources(ii)
+    if tuple(eta.shape) != (M, ht, wd):
+        _forget_sources(ii)
+        M = _num_sources(ii)
     if tuple(eta.shape) != (M, ht, wd):
         raise RuntimeError(f"eta must be [{M},{ht},{wd}] (one map per unique source keyframe), got {tuple(eta.shape)}")
     dzcov = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
