@@ -39,6 +39,8 @@ SIGNATURES = {
                            C.c_int, C.c_int, C.c_int, C.c_int64, C.c_float, C.c_float, C.c_float, c_f, C.c_void_p]),
     "dba_depth_cov": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
                                 C.c_int, C.c_int64, C.c_int, C.c_int, C.c_float, C.c_float, c_f, C.c_void_p]),
+    "dba_rel_pose_cov": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                   c_f, c_f, c_f, C.c_void_p]),
     "dba_reproject": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int, c_f, c_f,
                                 C.c_void_p]),
     "dba_cvx_upsample": (C.c_int, [C.c_void_p, c_f, c_f, C.c_int64, C.c_int, C.c_int, C.c_int, c_f, C.c_void_p]),

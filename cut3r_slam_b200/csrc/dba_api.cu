@@ -751,6 +751,22 @@ int dba_bi_inter(dba_ctx* ctx, const float* scales, const float* grid, int64_t M
   return 0;
 }
 
+int dba_rel_pose_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
+                     const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
+                     float* rel_out, float* cov_out, float* valid_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (E == 0) return 0;
+  if (!poses || !disps || !intrinsics || !targets || !weights || !ii || !jj || !rel_out || !cov_out || !valid_out)
+    return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_rel_pose(poses, disps, intrinsics, targets, weights, ii, jj, int(E), ht * wd, wd, rel_out, cov_out, valid_out,
+                     reinterpret_cast<cudaStream_t>(stream)), "rel_pose_cov");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
 int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
                   const int64_t* jj, int64_t E, int64_t N, int ht, int wd, float* coords_out, float* valid_out,
                   void* stream) {

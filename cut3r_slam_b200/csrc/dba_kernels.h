@@ -107,6 +107,9 @@ void cholesky_ldiag_layout(int* stride, int* linv_offset);   // per 32-block: wh
 size_t cov_scratch_floats(int n);
 cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* scratch,
                              size_t smem_cap, float* dzcov, cudaStream_t st);
+cudaError_t launch_rel_pose(const float* poses, const float* disps, const float* intr, const float* targets,
+                            const float* weights, const int64_t* ii, const int64_t* jj, int E, int HW, int wd,
+                            float* rel_out, float* cov_out, float* valid_out, cudaStream_t st);
 int jdsa_max_nodes();
 size_t jdsa_dynamic_smem(int ht, int wd);
 cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,

@@ -64,3 +64,34 @@ def upsample_disp(disp, mask):
     _check(disp, "disp", torch.float32, 4)
     B, num, ht, wd = disp.shape
     return cvx_upsample(disp.view(B * num, ht, wd, 1), mask).view(B, num, 8 * ht, 8 * wd)
+
+
+def add_rel_poses(poses, disps, intrinsics, ii, jj, target, weight):
+    """PGOBuffer.add_rel_poses (hislam2/pgo_buffer.py:85-123) without the buffer bookkeeping: returns the rows the
+    reference appends -- (ii, jj, rel_poses [n,7], rel_covs [n,6], valid_percent [n]) for the edges whose weight mask
+    passes (mean(weight > 0.1) > 1e-2).  target / weight in the FactorGraph layout [1,E,ht,wd,2] (or [E,ht,wd,2])."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if target.dim() == 5:
+        target, weight = target[0], weight[0]
+    for t, nm in ((target, "target"), (weight, "weight")):
+        if not t.is_cuda or t.dtype != torch.float32 or tuple(t.shape) != (E, ht, wd, 2):
+            raise RuntimeError(f"{nm} must be a float32 CUDA tensor [{E},{ht},{wd},2], got {tuple(t.shape)}")
+    tg = target.permute(0, 3, 1, 2).contiguous()           # the `ba` op layout [E,2,ht,wd] (depth_video.pyc cuda_ba@229-230)
+    wg = weight.permute(0, 3, 1, 2).contiguous()
+    rel = torch.empty((E, 7), dtype=torch.float32, device=poses.device)
+    cov = torch.empty((E, 6), dtype=torch.float32, device=poses.device)
+    val = torch.empty((E,), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_rel_pose_cov(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(tg), _ptr(wg),
+                                           _ptr(ii), _ptr(jj), E, N, ht, wd, _ptr(rel), _ptr(cov), _ptr(val),
+                                           C.c_void_p(stream)))
+    keep = val > 1e-2                                       # pgo_buffer.py:87-89
+    return ii[keep], jj[keep], rel[keep], cov[keep], val[keep]

@@ -108,6 +108,15 @@ int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const fl
                   int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, float lm, float ep, float* dzcov_out,
                   void* stream);
 
+/* ---- relative pose + diagonal covariance per loop-closure edge: PGOBuffer.add_rel_poses
+ * (hislam2/pgo_buffer.py:85-123).  For every edge e (no masking here: the caller drops edges
+ * with valid_out[e] <= 1e-2 as pgo_buffer.py:87-89 does): rel_out [E,7] = Exp(dx)^4 (G_jj G_ii^-1) with dx the
+ * Gauss-Newton step of the 6-dof reprojection problem at the current poses, cov_out [E,6] = diag(sigma^2 H^-1),
+ * valid_out [E] = mean(weight > 0.1).  targets / weights [E,2,ht,wd] (the `ba` layout); ii / jj DEVICE int64. */
+int dba_rel_pose_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* targets,
+                     const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int64_t N, int ht, int wd,
+                     float* rel_out, float* cov_out, float* valid_out, void* stream);
+
 /* ---- the elementwise steps either side of `ba` in FactorGraph.update
  * reproject(ii, jj) -> (coords, valid)  [hislam2/depth_video.pyc reproject@170-178 = projective_transform,
  *   hislam2/geom/projective_ops.py:44-74 with jacobian=False]: coords [E,ht,wd,2] = pixel of frame jj[e] that pixel
