@@ -49,7 +49,8 @@ k_proj_trans(const float* __restrict__ poses, const float* __restrict__ disps, c
     }
     __syncthreads();
     if (inb) {
-      for (int le = 0; le < nc; ++le) {
+#pragma unroll 4
+      for (int le = 0; le < nc; ++le) {                 // four edges' loads in flight per thread
         const float* tg = targets + int64_t(sedge[le]) * 2 * HW;
         const float* wg = weights + int64_t(sedge[le]) * 2 * HW;
         const float tx = __ldcs(tg + p), ty = __ldcs(tg + HW + p);
