@@ -761,7 +761,7 @@ int dba_rel_pose_cov(dba_ctx* ctx, const float* poses, const float* disps, const
     return fail_arg(ctx, "NULL argument");
   CK(cudaSetDevice(ctx->device), "cudaSetDevice");
   g_launch_count = 0;
-  CK(launch_rel_pose(poses, disps, intrinsics, targets, weights, ii, jj, int(E), ht * wd, wd, rel_out, cov_out, valid_out,
+  CK(launch_rel_pose(poses, disps, intrinsics, targets, weights, ii, jj, int(E), int(N), ht * wd, wd, rel_out, cov_out, valid_out,
                      reinterpret_cast<cudaStream_t>(stream)), "rel_pose_cov");
   ctx->last_launches = g_launch_count;
   return 0;
@@ -777,7 +777,7 @@ int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const fl
   if (!poses || !disps || !intrinsics || !ii || !jj || !coords_out || !valid_out) return fail_arg(ctx, "NULL argument");
   CK(cudaSetDevice(ctx->device), "cudaSetDevice");
   g_launch_count = 0;
-  CK(launch_reproject(poses, disps, intrinsics, ii, jj, int(E), ht * wd, wd, coords_out, valid_out,
+  CK(launch_reproject(poses, disps, intrinsics, ii, jj, int(E), int(N), ht * wd, wd, coords_out, valid_out,
                       reinterpret_cast<cudaStream_t>(stream)), "reproject");
   ctx->last_launches = g_launch_count;
   return 0;

@@ -89,6 +89,107 @@ k_linv(const float* __restrict__ L, int ld, int n, const float* __restrict__ Ldi
   }
 }
 
+// Right-looking variant for n <= 32 * LINV_RL_MAX: the running sums T_r = sum_m L[r][m] W[m][c] of ALL later block
+// rows live in shared memory and receive one term per step, so the chain per step is only
+//   warp 0: W[m][c] = -L_mm^-1 T_m  ->  barrier  ->  warp 0: T_{m+1} += L[m+1][m] W[m][c]
+// (the other warps update the rows further down meanwhile; L blocks and the next L_mm^-1 are independent of the chain).
+constexpr int LINV_RL_MAX = 40;                              // block rows whose T fit next to the staging buffers
+constexpr int RL_T = 512, RL_W = RL_T / 32;
+
+__global__ void __launch_bounds__(RL_T, 1)
+k_linv_rl(const float* __restrict__ L, int ld, int n, const float* __restrict__ Ldiag, int ld_stride, int ld_linv,
+          float* __restrict__ W, int ldw) {
+  extern __shared__ __align__(16) float rsm[];
+  const int nkb = (n + CB - 1) / CB;
+  const int c = blockIdx.x, c0 = c * CB;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nrow = nkb - c - 1;                              // block rows below the diagonal block
+  float* sWm = rsm;                                          // [2][32][32]   W[m][c], k-major
+  float* sLi = sWm + 2 * CB * CB;                            // [3][32][36]   L_mm^-1, fetched two steps ahead
+  float* sLw = sLi + 3 * CB * (CB + 4);                      // [RL_W][32][36] the warp's L[r][m] block
+  float* sT = sLw + RL_W * CB * (CB + 4);                       // [nrow][32][32]
+  for (int e = tid; e < nrow * CB * CB; e += RL_T) sT[e] = 0.f;
+  auto load_linv = [&](int m, int buf) {                     // by one warp: 32 rows x 32 floats
+    for (int i = 0; i < CB; ++i)
+      sLi[(buf * CB + i) * (CB + 4) + lane] = __ldg(Ldiag + int64_t(m) * ld_stride + ld_linv + i * CB + lane);
+  };
+  if (warp == 1) load_linv(c, 0);
+  if (warp == 2 && c + 1 < nkb) load_linv(c + 1, 1);
+  __syncthreads();
+  for (int m = c; m < nkb; ++m) {
+    const int buf = (m - c) & 1;
+    float* Wm = sWm + buf * CB * CB;
+    if (warp == 0) {
+      // W[m][c]: lane = column j; the diagonal step takes L_cc^-1 itself
+      const float* Li = sLi + ((m - c) % 3) * CB * (CB + 4);
+      if (m == c) {
+#pragma unroll 8
+        for (int i = 0; i < CB; ++i) {
+          const float v = Li[i * (CB + 4) + lane];
+          Wm[i * CB + lane] = v;
+          W[int64_t(c0 + i) * ldw + c0 + lane] = v;
+        }
+      } else {
+        const float* T = sT + size_t(m - c - 1) * CB * CB;
+        float tk[CB];
+#pragma unroll
+        for (int k = 0; k < CB; ++k) tk[k] = T[k * CB + lane];
+        // k outermost: 32 independent accumulators, so the broadcast loads of consecutive rows pipeline
+        float acc[CB];
+#pragma unroll
+        for (int i = 0; i < CB; ++i) acc[i] = 0.f;
+#pragma unroll
+        for (int k = 0; k < CB; k += 4) {
+#pragma unroll
+          for (int i = 0; i < CB; ++i) {
+            const float4 l4 = *reinterpret_cast<const float4*>(Li + i * (CB + 4) + k);
+            acc[i] = fmaf(l4.x, tk[k], acc[i]); acc[i] = fmaf(l4.y, tk[k + 1], acc[i]);
+            acc[i] = fmaf(l4.z, tk[k + 2], acc[i]); acc[i] = fmaf(l4.w, tk[k + 3], acc[i]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < CB; ++i) {
+          Wm[i * CB + lane] = -acc[i];
+          W[int64_t(m * CB + i) * ldw + c0 + lane] = -acc[i];
+        }
+      }
+    }
+    __syncthreads();                                         // W[m][c] visible; the other sWm / sLi buffers are free
+    if (warp == RL_W - 1 && m + 2 < nkb) load_linv(m + 2, (m + 2 - c) % 3);   // read after the barrier of step m + 1
+    // T_r += L[r][m] W[m][c] for the rows below, dealt over the warps (warp 0 takes r = m + 1: the chain)
+    float wk[CB];
+#pragma unroll
+    for (int k = 0; k < CB; ++k) wk[k] = Wm[k * CB + lane];
+    float* Lw = sLw + warp * CB * (CB + 4);
+    for (int r = m + 1 + warp; r < nkb; r += RL_W) {
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < CB; ++i) Lw[i * (CB + 4) + lane] = L_at(L, ld, n, r * CB + i, m * CB + lane);
+      __syncwarp();
+      float* T = sT + size_t(r - c - 1) * CB * CB;
+      float acc[CB];
+#pragma unroll
+      for (int i = 0; i < CB; ++i) acc[i] = T[i * CB + lane];
+#pragma unroll
+      for (int k = 0; k < CB; k += 4) {
+#pragma unroll
+        for (int i = 0; i < CB; ++i) {
+          const float4 l4 = *reinterpret_cast<const float4*>(Lw + i * (CB + 4) + k);
+          acc[i] = fmaf(l4.x, wk[k], acc[i]); acc[i] = fmaf(l4.y, wk[k + 1], acc[i]);
+          acc[i] = fmaf(l4.z, wk[k + 2], acc[i]); acc[i] = fmaf(l4.w, wk[k + 3], acc[i]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < CB; ++i) T[i * CB + lane] = acc[i];
+    }
+    // no barrier here: T_{m+1} belongs to warp 0 itself, everything else is protected by the barrier of step m + 1
+  }
+}
+
+size_t linv_rl_smem(int nkb) {
+  return (size_t(2) * CB * CB + 3 * CB * (CB + 4) + RL_W * CB * (CB + 4) + size_t(nkb > 1 ? nkb - 1 : 0) * CB * CB) * sizeof(float);
+}
+
 // Sinv = W^T W, lower tiles (a >= b) mirrored.  W is lower triangular by blocks: rows >= a only.
 __global__ void __launch_bounds__(256)
 k_wtw(const float* __restrict__ W, int ldw, int nkb, float* __restrict__ Sinv) {
@@ -275,7 +376,13 @@ cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Wor
   if (n > 0) {
     int ld_stride = 0, ld_linv = 0;
     cholesky_ldiag_layout(&ld_stride, &ld_linv);
-    k_linv<<<nkb, 256, 0, st>>>(ws.Lm, ws.ldA, n, ws.Ldiag, ld_stride, ld_linv, W, npad);
+    if (nkb <= LINV_RL_MAX && linv_rl_smem(nkb) + 1024 <= smem_cap) {
+      err = cudaFuncSetAttribute(k_linv_rl, cudaFuncAttributeMaxDynamicSharedMemorySize, int(linv_rl_smem(nkb)));
+      if (err != cudaSuccess) return err;
+      k_linv_rl<<<nkb, RL_T, linv_rl_smem(nkb), st>>>(ws.Lm, ws.ldA, n, ws.Ldiag, ld_stride, ld_linv, W, npad);
+    } else {
+      k_linv<<<nkb, 256, 0, st>>>(ws.Lm, ws.ldA, n, ws.Ldiag, ld_stride, ld_linv, W, npad);
+    }
     k_wtw<<<nkb * (nkb + 1) / 2, 256, 0, st>>>(W, npad, nkb, Sinv);
     g_launch_count += 2;
   }

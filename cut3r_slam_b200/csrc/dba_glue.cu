@@ -19,11 +19,19 @@ constexpr int RP_T = 256;
 // grid (nsplit, E): one relative pose per CTA, the CTA strides over its share of the pixels
 __global__ void __launch_bounds__(RP_T)
 k_reproject(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
-            const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int HW, int wd, float2* __restrict__ coords,
-            float* __restrict__ valid) {
+            const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int N, int HW, int wd,
+            float2* __restrict__ coords, float* __restrict__ valid) {
   __shared__ float sRt[12];
   const int e = blockIdx.y;
-  const int i = int(ii[e]), j = int(jj[e]);
+  const int64_t i64 = ii[e], j64 = jj[e];
+  if (i64 < 0 || i64 >= N || j64 < 0 || j64 >= N) {        // an index outside the frame buffer: defined output, no read
+    for (int p = blockIdx.x * RP_T + threadIdx.x; p < HW; p += gridDim.x * RP_T) {
+      coords[int64_t(e) * HW + p] = make_float2(0.f, 0.f);
+      valid[int64_t(e) * HW + p] = 0.f;
+    }
+    return;
+  }
+  const int i = int(i64), j = int(j64);
   if (threadIdx.x == 0) relative_pose_Rt(poses, i, j, sRt);
   __syncthreads();
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
@@ -160,7 +168,7 @@ k_cvx_upsample_flat(const float* __restrict__ data, const float* __restrict__ ma
 }  // namespace
 
 cudaError_t launch_reproject(const float* poses, const float* disps, const float* intr, const int64_t* ii,
-                             const int64_t* jj, int E, int HW, int wd, float* coords, float* valid, cudaStream_t st) {
+                             const int64_t* jj, int E, int N, int HW, int wd, float* coords, float* valid, cudaStream_t st) {
   if (E <= 0) return cudaSuccess;
   // about 16 CTAs per SM in total; an edge is never split finer than one pixel per thread
   int nsplit = (148 * 16 + E - 1) / E;
@@ -168,7 +176,7 @@ cudaError_t launch_reproject(const float* poses, const float* disps, const float
   if (nsplit > maxsplit) nsplit = maxsplit;
   if (nsplit < 1) nsplit = 1;
   dim3 grid(nsplit, E);
-  k_reproject<<<grid, RP_T, 0, st>>>(poses, disps, intr, ii, jj, HW, wd, reinterpret_cast<float2*>(coords), valid);
+  k_reproject<<<grid, RP_T, 0, st>>>(poses, disps, intr, ii, jj, N, HW, wd, reinterpret_cast<float2*>(coords), valid);
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -100,7 +100,7 @@ cudaError_t launch_proj_trans(const float* poses, const float* disps, const floa
 cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int HW, int hs, int ws, float* vals,
                             float* J, cudaStream_t st);
 cudaError_t launch_reproject(const float* poses, const float* disps, const float* intr, const int64_t* ii,
-                             const int64_t* jj, int E, int HW, int wd, float* coords, float* valid, cudaStream_t st);
+                             const int64_t* jj, int E, int N, int HW, int wd, float* coords, float* valid, cudaStream_t st);
 cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int ht, int wd, int dim, float* up,
                                 cudaStream_t st);
 void cholesky_ldiag_layout(int* stride, int* linv_offset);   // per 32-block: where L_kk^-1 (row-major 32x32) sits
@@ -108,7 +108,7 @@ size_t cov_scratch_floats(int n);
 cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* scratch,
                              size_t smem_cap, float* dzcov, cudaStream_t st);
 cudaError_t launch_rel_pose(const float* poses, const float* disps, const float* intr, const float* targets,
-                            const float* weights, const int64_t* ii, const int64_t* jj, int E, int HW, int wd,
+                            const float* weights, const int64_t* ii, const int64_t* jj, int E, int N, int HW, int wd,
                             float* rel_out, float* cov_out, float* valid_out, cudaStream_t st);
 int jdsa_max_nodes();
 size_t jdsa_dynamic_smem(int ht, int wd);

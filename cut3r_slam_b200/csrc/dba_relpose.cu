@@ -56,11 +56,18 @@ __device__ __forceinline__ void block_reduce(float (&v)[N], float* swarp, float*
 __global__ void __launch_bounds__(RPT)
 k_rel_pose(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
            const float* __restrict__ targets, const float* __restrict__ weights, const int64_t* __restrict__ ii,
-           const int64_t* __restrict__ jj, int HW, int wd, float* __restrict__ rel_out, float* __restrict__ cov_out,
+           const int64_t* __restrict__ jj, int N, int HW, int wd, float* __restrict__ rel_out, float* __restrict__ cov_out,
            float* __restrict__ valid_out) {
   __shared__ float sRt[12], swarp[(RPT / 32) * NRED], sred[NRED], sdx[6], sHd[6];
   const int e = blockIdx.x, tid = threadIdx.x;
-  const int i = int(ii[e]), j = int(jj[e]);
+  const int64_t i64 = ii[e], j64 = jj[e];
+  if (i64 < 0 || i64 >= N || j64 < 0 || j64 >= N) {        // outside the frame buffer: the edge is reported as masked out
+    if (tid < 7) rel_out[int64_t(e) * 7 + tid] = (tid == 6) ? 1.f : 0.f;
+    if (tid < 6) cov_out[int64_t(e) * 6 + tid] = 0.f;
+    if (tid == 0) valid_out[e] = 0.f;
+    return;
+  }
+  const int i = int(i64), j = int(j64);
   if (tid == 0) relative_pose_Rt(poses, i, j, sRt);
   __syncthreads();
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
@@ -156,10 +163,10 @@ k_rel_pose(const float* __restrict__ poses, const float* __restrict__ disps, con
 }  // namespace
 
 cudaError_t launch_rel_pose(const float* poses, const float* disps, const float* intr, const float* targets,
-                            const float* weights, const int64_t* ii, const int64_t* jj, int E, int HW, int wd,
+                            const float* weights, const int64_t* ii, const int64_t* jj, int E, int N, int HW, int wd,
                             float* rel_out, float* cov_out, float* valid_out, cudaStream_t st) {
   if (E <= 0) return cudaSuccess;
-  k_rel_pose<<<E, RPT, 0, st>>>(poses, disps, intr, targets, weights, ii, jj, HW, wd, rel_out, cov_out, valid_out);
+  k_rel_pose<<<E, RPT, 0, st>>>(poses, disps, intr, targets, weights, ii, jj, N, HW, wd, rel_out, cov_out, valid_out);
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -121,7 +121,8 @@ int dba_rel_pose_cov(dba_ctx* ctx, const float* poses, const float* disps, const
  * reproject(ii, jj) -> (coords, valid)  [hislam2/depth_video.pyc reproject@170-178 = projective_transform,
  *   hislam2/geom/projective_ops.py:44-74 with jacobian=False]: coords [E,ht,wd,2] = pixel of frame jj[e] that pixel
  *   (y,x) of frame ii[e] lands on, valid [E,ht,wd,1] = 1 where the transformed depth exceeds MIN_DEPTH = 0.2.
- *   ii / jj: DEVICE int64 in [0, N) (not validated: no host round trip on this path). */
+ *   ii / jj: DEVICE int64; an edge with an index outside [0, N) gets coords = 0, valid = 0 (checked on the device:
+ *   no host round trip on this path). */
 int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
                   const int64_t* jj, int64_t E, int64_t N, int ht, int wd, float* coords_out, float* valid_out,
                   void* stream);

@@ -98,3 +98,7 @@ def test_reproject_backend_size_matches_oracle():
     assert gl.reproject(g.poses, g.disps, g.intrinsics, e, e)[0].shape == (1, 0, ht, wd, 2)
     with pytest.raises(RuntimeError):
         gl.reproject(g.poses, g.disps, g.intrinsics, ii.int(), ii.int())
+    # an index outside the frame buffer is answered with valid = 0 instead of an out-of-bounds read
+    bad = torch.tensor([0, 10 ** 6, -1], device="cuda")
+    c, v = gl.reproject(g.poses, g.disps, g.intrinsics, torch.zeros(3, dtype=torch.long, device="cuda"), bad)
+    assert float(v[0, 0].min()) == 1.0 and float(v[0, 1:].abs().max()) == 0.0 and float(c[0, 1:].abs().max()) == 0.0
