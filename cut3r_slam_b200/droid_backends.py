@@ -338,12 +338,9 @@ def JDSA(target, weight, eta, poses, disps, intrinsics, disps_prior, dscales, ii
     for t, nm in ((target, "target"), (weight, "weight")):
         if tuple(t.shape) != (E, 2, ht, wd):
             raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
-    M = _num_sources(ii)
-    if tuple(eta.shape) != (M, ht, wd):
-        _forget_sources(ii)
-        M = _num_sources(ii)
-    if tuple(eta.shape) != (M, ht, wd):
-        raise RuntimeError(f"eta must be [{M},{ht},{wd}] (one map per unique source keyframe), got {tuple(eta.shape)}")
+    M = eta.shape[0]                     # one map per unique source keyframe: the library counts them and rejects a mismatch
+    if tuple(eta.shape[1:]) != (ht, wd):
+        raise RuntimeError(f"eta must be [M,{ht},{wd}] (one map per unique source keyframe), got {tuple(eta.shape)}")
     dzcov = torch.empty((M, ht, wd), dtype=torch.float32, device=poses.device)
     ctx = context(poses.device)
     with torch.cuda.device(poses.device):
