@@ -104,6 +104,7 @@ def test_jdsa_matches_reference_golden(name):
     dict(P=12, E=60, ht=24, wd=32, iters=1, t0=1, r=3, seed=23, hs=1, ws=5, alpha=0.02),    # degenerate grid rows
     dict(P=8, E=30, ht=16, wd=20, iters=1, t0=1, r=2, seed=24, hs=4, ws=1, alpha=0.02),
     dict(P=8, E=30, ht=16, wd=20, iters=1, t0=1, r=2, seed=25, hs=1, ws=1, alpha=0.05),     # one global scale
+    dict(P=6, E=20, ht=5, wd=6, iters=1, t0=1, r=2, seed=26, hs=8, ws=8, alpha=0.02),       # more nodes than pixels
 ])
 def test_jdsa_matches_oracle(kw):
     p, scales, prior, alpha = make_case(kw)
