@@ -461,11 +461,14 @@ k_backsolve_smem(const float* __restrict__ Lm, const float* __restrict__ Ldiag, 
   auto prefetch = [&](int kb) {          // slab rows k0..k0+31 (columns < k0) and L_kk^-1 of block kb
     const int k0 = kb * NB, nb = min(NB, n - k0);
     float* dst = slab + (kb & 1) * NB * W;
+    // thread = (row tid / 16, chunk lane tid % 16): no index division in the copy loop -- this kernel is bound by the
+    // instructions its one CTA issues (ncu: issue slots 52 % busy, 45 % of the instructions were this loop's)
     const int cpr = k0 >> 2;             // 16-byte chunks per row
-    for (int i = tid; i < NB * cpr; i += BSN) {
-      const int r = i / cpr, ch = i - r * cpr;
-      cp_async16(dst + r * W + ch * 4, Lm + int64_t(k0 + r) * ld + ch * 4, r < nb);
-    }
+    const int r = tid >> 4;
+    const float* src = Lm + int64_t(k0 + r) * ld;
+    float* drow = dst + r * W;
+    const bool rv = r < nb;
+    for (int ch = tid & 15; ch < cpr; ch += 16) cp_async16(drow + ch * 4, src + ch * 4, rv);
     if (tid < NB * NB / 4)
       cp_async16(sLi + (kb & 1) * NB * NB + tid * 4, Ldiag + int64_t(kb) * LD_STRIDE + LD_LINV + tid * 4, true);
     asm volatile("cp.async.commit_group;\n" ::: "memory");
