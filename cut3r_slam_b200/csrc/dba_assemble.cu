@@ -223,7 +223,7 @@ k_backsub(const float* __restrict__ poses, float* __restrict__ disps, const floa
           const float* __restrict__ wv, const float* __restrict__ dx, float* __restrict__ dz, int HW, int wd,
           int ntiles, int t0, int Pp) {
   __shared__ float sRt[BS_CHUNK * 12];
-  __shared__ float sdx[BS_CHUNK * 6];
+  __shared__ float sMc[BS_CHUNK * 12];   // per edge: M (3x3) and c (3) of u = M X0 + d c, see below
   __shared__ int sedge[BS_CHUNK];
   const int m = blockIdx.x / ntiles, tile = blockIdx.x % ntiles;
   const int tid = threadIdx.x;
@@ -240,37 +240,56 @@ k_backsub(const float* __restrict__ poses, float* __restrict__ disps, const floa
 #pragma unroll
     for (int i = 0; i < 6; ++i) tk[i] = dx[(k - t0) * 6 + i];
   }
-  // z = d tau_k + phi_k x X0
-  const float zx = dd * tk[0] + (tk[4] * 1.f - tk[5] * yy);
-  const float zy = dd * tk[1] + (tk[5] * xx - tk[3] * 1.f);
-  const float zz = dd * tk[2] + (tk[3] * yy - tk[4] * xx);
+  // E^T dx per edge-pixel is h . u with u = d tau_j + phi_j x X1 - R z, z = d tau_k + phi_k x X0, X1 = R X0 + d t.
+  // Everything but h is linear in (X0, d) with per-edge coefficients:
+  //   u = M X0 + d c ,  M = [phi_j]x R - R [phi_k]x ,  c = tau_j + phi_j x t - R tau_k
+  // built once per edge (12 floats, like Rt) instead of ~30 FMAs per edge-pixel.
   float etdx = 0.f;
   for (int c0 = 0; c0 < deg; c0 += BS_CHUNK) {
     const int nc = min(BS_CHUNK, deg - c0);
     __syncthreads();
     for (int le = tid; le < nc; le += BS_T) {
       const int j = cj[e0 + c0 + le];
-      relative_pose_Rt(poses, k, j, sRt + 12 * le);
+      float Rt[12];
+      relative_pose_Rt(poses, k, j, Rt);
       const bool opt = (j - t0 >= 0 && j - t0 < Pp);
+      float tj[6];
 #pragma unroll
-      for (int i = 0; i < 6; ++i) sdx[le * 6 + i] = opt ? dx[(j - t0) * 6 + i] : 0.f;
+      for (int i = 0; i < 6; ++i) tj[i] = opt ? dx[(j - t0) * 6 + i] : 0.f;
+      float* Mc = sMc + 12 * le;
+#pragma unroll
+      for (int col = 0; col < 3; ++col) {
+        // column `col` of [phi_j]x R = phi_j x R[:,col] ; column `col` of R [phi_k]x = R (phi_k x e_col)
+        const float r0 = Rt[col], r1 = Rt[3 + col], r2 = Rt[6 + col];
+        const float ax = tj[4] * r2 - tj[5] * r1, ay = tj[5] * r0 - tj[3] * r2, az = tj[3] * r1 - tj[4] * r0;
+        // phi_k x e_col
+        const float px_ = (col == 0) ? 0.f : (col == 1 ? -tk[5] : tk[4]);
+        const float py_ = (col == 0) ? tk[5] : (col == 1 ? 0.f : -tk[3]);
+        const float pz_ = (col == 0) ? -tk[4] : (col == 1 ? tk[3] : 0.f);
+        Mc[0 + col] = ax - (Rt[0] * px_ + Rt[1] * py_ + Rt[2] * pz_);
+        Mc[3 + col] = ay - (Rt[3] * px_ + Rt[4] * py_ + Rt[5] * pz_);
+        Mc[6 + col] = az - (Rt[6] * px_ + Rt[7] * py_ + Rt[8] * pz_);
+      }
+      Mc[9] = tj[0] + (tj[4] * Rt[11] - tj[5] * Rt[10]) - (Rt[0] * tk[0] + Rt[1] * tk[1] + Rt[2] * tk[2]);
+      Mc[10] = tj[1] + (tj[5] * Rt[9] - tj[3] * Rt[11]) - (Rt[3] * tk[0] + Rt[4] * tk[1] + Rt[5] * tk[2]);
+      Mc[11] = tj[2] + (tj[3] * Rt[10] - tj[4] * Rt[9]) - (Rt[6] * tk[0] + Rt[7] * tk[1] + Rt[8] * tk[2]);
+#pragma unroll
+      for (int i = 0; i < 12; ++i) sRt[12 * le + i] = Rt[i];
       sedge[le] = cedge[e0 + c0 + le];
     }
     __syncthreads();
     if (inb) {
       for (int le = 0; le < nc; ++le) {
         const float* Rt = sRt + 12 * le;
-        const float* tj = sdx + 6 * le;
+        const float* Mc = sMc + 12 * le;
         const float* wg = weights + int64_t(sedge[le]) * 2 * HW;
         const float wx = __ldcs(wg + p), wy = __ldcs(wg + HW + p);
         const Proj pr = project(Rt, xx, yy, dd, fx, fy, cx, cy);
         const float a0 = kWeightScale * (pr.valid * wx) * pr.jz0, a1 = kWeightScale * (pr.valid * wy) * pr.jz1;
         const float hx = a0 * pr.a0, hy = a1 * pr.b1, hz = a0 * pr.c0 + a1 * pr.c1;
-        const float X = pr.X1.x, Y = pr.X1.y, Z = pr.X1.z;
-        // u = d tau_j + phi_j x X1 - R z
-        const float ux = dd * tj[0] + (tj[4] * Z - tj[5] * Y) - (Rt[0] * zx + Rt[1] * zy + Rt[2] * zz);
-        const float uy = dd * tj[1] + (tj[5] * X - tj[3] * Z) - (Rt[3] * zx + Rt[4] * zy + Rt[5] * zz);
-        const float uz = dd * tj[2] + (tj[3] * Y - tj[4] * X) - (Rt[6] * zx + Rt[7] * zy + Rt[8] * zz);
+        const float ux = Mc[0] * xx + Mc[1] * yy + Mc[2] + Mc[9] * dd;
+        const float uy = Mc[3] * xx + Mc[4] * yy + Mc[5] + Mc[10] * dd;
+        const float uz = Mc[6] * xx + Mc[7] * yy + Mc[8] + Mc[11] * dd;
         etdx += hx * ux + hy * uy + hz * uz;
       }
     }
