@@ -7,8 +7,9 @@
 //   * converts the fp32 panel to two tf32 operands hi = tf32(v), lo = v - hi, written by its own
 //     threads (st.shared) straight into the SWIZZLE_128B layout the tensor core reads;
 //   * one thread issues 24 tcgen05.mma (kind::tf32, M = 128, N = 16*ceil((R+1)/16), fp32 accumulate
-//     in TMEM): hi hi^T into accumulator 1, hi lo^T + lo hi^T into accumulator 2 ("3xTF32": ~22
-//     mantissa bits; the small cross terms get their own accumulator);
+//     in TMEM) into one accumulator: the sixteen cross terms hi lo^T + lo hi^T first, then the eight
+//     hi hi^T steps ("3xTF32": ~22 mantissa bits; the truncating TMEM adds of the small terms act on a
+//     small accumulator, the main chain is as long as with a separate accumulator);
 //   * the MMAs run while the SIMT pipes do phases 1-2 of the next tile.
 // TMEM accumulation is NOT round-to-nearest (measured: a 3328-pixel chain loses 4e-5 relative), so
 // every tile starts fresh accumulators and the per-tile results are added into fp32 registers
@@ -32,8 +33,7 @@ constexpr int KB = T / 32;             // 32-pixel K-blocks per tile
 constexpr int BS = 6 * T;              // floats per staged panel block (6 E rows)
 constexpr int PS = 5 * T + 8;          // floats per warp of the per-pixel partial sums (ck, wk, G): +8 bank spread
 constexpr uint32_t TILE = TILE_BYTES_128;
-constexpr int ACC2 = 128;              // TMEM column of the cross-term accumulator
-constexpr int TMEM_COLS = 256;
+constexpr int TMEM_COLS = 128;         // one fp32 accumulator, N <= 128 columns
 
 // float region after the two operand tiles:
 //   sRt [deg,12] | sHacc [deg,32] | ssq [T] | ssw [T] | spx [2][3][T] | spart [NW][PS] | staging [(deg+1), BS] |
@@ -207,12 +207,11 @@ k_linearize_tc(const LinParams P) {
     for (int gi = 0; gi < 4; ++gi) {
       const int g = 2 * gi + h;
       if (g < ngroups && (16 * g <= maxcol || g == gw)) {       // warp-uniform
-        uint32_t v1[16], v2[16];
+        uint32_t v1[16];
         tmem_ld16(tmem + tlane + 16 * g, v1);
-        tmem_ld16(tmem + tlane + ACC2 + 16 * g, v2);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) tot[gi][j] += __uint_as_float(v1[j]) + __uint_as_float(v2[j]);
+        for (int j = 0; j < 16; ++j) tot[gi][j] += __uint_as_float(v1[j]);
       }
     }
   };
@@ -364,16 +363,23 @@ k_linearize_tc(const LinParams P) {
       tc_fence_after_sync();
       const uint32_t idesc = make_idesc_tf32(128, N);
       const uint32_t ah = smem_u32(hi), al = smem_u32(lo);
+      // the small cross terms first, so that the truncating TMEM adds act on a small accumulator;
+      // the eight hi hi^T steps follow (the same chain length as a separate main accumulator)
 #pragma unroll
       for (int kb = 0; kb < KB; ++kb)
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
           const uint64_t dl = make_desc_sw128(al + kb * TILE + ks * 32);
-          const bool first = (kb == 0 && ks == 0);
-          mma_tf32_ss(tmem, dh, dh, idesc, !first);
-          mma_tf32_ss(tmem + ACC2, dh, dl, idesc, !first);
-          mma_tf32_ss(tmem + ACC2, dl, dh, idesc, true);
+          mma_tf32_ss(tmem, dh, dl, idesc, !(kb == 0 && ks == 0));
+          mma_tf32_ss(tmem, dl, dh, idesc, true);
+        }
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
+          mma_tf32_ss(tmem, dh, dh, idesc, true);
         }
       mma_commit(&mbar);
     }
