@@ -32,8 +32,13 @@ constexpr int T = 32 * PPL;            // pixels per tile = K per flush
 constexpr int KB = T / 32;             // 32-pixel K-blocks per tile
 constexpr int BS = 6 * T;              // floats per staged panel block (6 E rows)
 constexpr int PS = 5 * T + 8;          // floats per warp of the per-pixel partial sums (ck, wk, G): +8 bank spread
-constexpr uint32_t TILE = TILE_BYTES_128;
 constexpr int TMEM_COLS = 128;         // one fp32 accumulator, N <= 128 columns
+// WIDE variant (out-degree 21..25, R + 1 <= 160 panel rows): operand tiles of 256 rows, a second product
+// D2 = P'[128..255] P'[0..N2)^T (N2 <= 160) in TMEM columns 128.., whose 32 meaningful lanes belong to the
+// warps of lane quarter 0; one CTA per SM (80 more accumulator registers in those warps).
+constexpr int WIDE_MAXDEG = 25;
+constexpr int TMEM_COLS_WIDE = 512;
+constexpr int D2COL = 128;
 
 // float region after the two operand tiles:
 //   sRt [deg,12] | sHacc [deg,32] | ssq [T] | ssw [T] | spx [2][3][T] | spart [NW][PS] | staging [(deg+1), BS] |
@@ -126,9 +131,10 @@ __device__ __forceinline__ void tc_load(const float* __restrict__ tg, const floa
   }
 }
 
-template <bool STREAM>
-__global__ void __launch_bounds__(NT, 2)
+template <bool STREAM, bool WIDE>
+__global__ void __launch_bounds__(NT, WIDE ? 1 : 2)
 k_linearize_tc(const LinParams P) {
+  constexpr uint32_t TILE = WIDE ? TILE_BYTES_256 : TILE_BYTES_128;
   // dynamic shared memory only (no static __shared__), so the window starts 1024-byte aligned as the
   // SWIZZLE_128B operand tiles require; all pointers stay in the shared address space (LDS / STS)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -156,7 +162,8 @@ k_linearize_tc(const LinParams P) {
   const int nblk = deg + 1;
   const int npairs = nblk * (nblk + 1) / 2;
   const int R = 6 * nblk;                   // panel rows; row R carries w
-  const int N = (R + 1 + 15) & ~15;
+  const int N2 = (R + 1 + 15) & ~15;         // columns that hold data (incl. the w row)
+  const int N = WIDE ? 128 : N2;             // columns of the first product
   const int HW = P.HW;
   const float fx = P.intr[0], fy = P.intr[1], cx = P.intr[2], cy = P.intr[3];
   const int tile_lo = s * P.tiles_per_split;
@@ -182,7 +189,7 @@ k_linearize_tc(const LinParams P) {
     float4* z = reinterpret_cast<float4*>(smem_raw);
     for (int i = tid; i < int(2 * KB * TILE / 16); i += NT) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  if (warp == 0) tmem_alloc(&tmem_s, TMEM_COLS);
+  if (warp == 0) tmem_alloc(&tmem_s, WIDE ? TMEM_COLS_WIDE : TMEM_COLS);
   if (tid == 0) mbar_init(&mbar, 1);
   tc_fence_before_sync();
   __syncthreads();
@@ -201,6 +208,13 @@ k_linearize_tc(const LinParams P) {
   for (int gi = 0; gi < 4; ++gi)
 #pragma unroll
     for (int j = 0; j < 16; ++j) tot[gi][j] = 0.f;
+  // WIDE: rows 128 + lane of the second product, column groups g = 2*gi + h (warps 0 and 4 only)
+  constexpr int NG2 = WIDE ? 5 : 1;
+  float tot2[NG2][16];
+#pragma unroll
+  for (int gi = 0; gi < NG2; ++gi)
+#pragma unroll
+    for (int j = 0; j < 16; ++j) tot2[gi][j] = 0.f;
 
   auto flush = [&]() {
 #pragma unroll
@@ -212,6 +226,19 @@ k_linearize_tc(const LinParams P) {
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 16; ++j) tot[gi][j] += __uint_as_float(v1[j]);
+      }
+    }
+    if (WIDE && qd == 0) {
+#pragma unroll
+      for (int gi = 0; gi < NG2; ++gi) {
+        const int g = 2 * gi + h;
+        if (16 * g < N2) {                                        // warp-uniform
+          uint32_t v1[16];
+          tmem_ld16(tmem + D2COL + 16 * g, v1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) tot2[gi][j] += __uint_as_float(v1[j]);
+        }
       }
     }
   };
@@ -381,6 +408,28 @@ k_linearize_tc(const LinParams P) {
           const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
           mma_tf32_ss(tmem, dh, dh, idesc, true);
         }
+      if (WIDE) {   // rows 128.. against all rows: A = the tile's second 128 rows (16 KB further), B = rows [0, N2)
+        const uint32_t idesc2 = make_idesc_tf32(128, N2);
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
+            const uint64_t dl = make_desc_sw128(al + kb * TILE + ks * 32);
+            const uint64_t dh2 = make_desc_sw128(ah + kb * TILE + TILE_BYTES_128 + ks * 32);
+            const uint64_t dl2 = make_desc_sw128(al + kb * TILE + TILE_BYTES_128 + ks * 32);
+            mma_tf32_ss(tmem + D2COL, dh2, dl, idesc2, !(kb == 0 && ks == 0));
+            mma_tf32_ss(tmem + D2COL, dl2, dh, idesc2, true);
+          }
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
+            const uint64_t dh2 = make_desc_sw128(ah + kb * TILE + TILE_BYTES_128 + ks * 32);
+            mma_tf32_ss(tmem + D2COL, dh2, dh, idesc2, true);
+          }
+      }
       mma_commit(&mbar);
     }
     pending = true;
@@ -415,8 +464,29 @@ k_linearize_tc(const LinParams P) {
       }
     }
   }
+  if (WIDE && qd == 0) {
+    const int row2 = 128 + lane;
+    const int A = row2 / 6, ri = row2 - A * 6;
+    float* Sdst = P.Spart + slab0 + int64_t(A) * (A + 1) / 2 * 36 + ri * 6;
+#pragma unroll
+    for (int gi = 0; gi < NG2; ++gi) {
+      const int g = 2 * gi + h;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int c = 16 * g + j;
+        if (c < R) {
+          if (row2 < R) {
+            const int B = c / 6, cj = c - B * 6;
+            if (B <= A) Sdst[B * 36 + cj] = tot2[gi][j];
+          } else if (row2 == R) {
+            P.vEpart[vE0 + c] = tot2[gi][j];       // row R = sum_p Q w E[c,p] (the product is symmetric)
+          }
+        }
+      }
+    }
+  }
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, TMEM_COLS);
+  if (warp == 0) tmem_dealloc(tmem, WIDE ? TMEM_COLS_WIDE : TMEM_COLS);
 #undef mbar
 #undef tmem_s
 }
@@ -425,12 +495,15 @@ k_linearize_tc(const LinParams P) {
 
 int g_tc_stream_mode = -1;   // -1 auto, 0 L2-resident loads, 1 evict-first loads ("stream_inputs" option)
 
-size_t linearize_tc_smem_bytes(int degmax) { return 2 * KB * TILE + tc_float_region(degmax) * sizeof(float) + 32; }
+size_t linearize_tc_smem_bytes(int degmax, bool wide) {
+  return 2 * KB * (wide ? TILE_BYTES_256 : TILE_BYTES_128) + tc_float_region(degmax) * sizeof(float) + 32;
+}
 int linearize_tc_max_degree() { return 20; }
+int linearize_tc_wide_max_degree() { return WIDE_MAXDEG; }
 int linearize_tc_ppl() { return PPL; }
 
 cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
-                                const int32_t* kf_list, int nkf, int degmax, cudaStream_t st) {
+                                const int32_t* kf_list, int nkf, int degmax, bool wide, cudaStream_t st) {
   if (nkf == 0) return cudaSuccess;
   LinParams P;
   P.poses = in.poses; P.disps = in.disps; P.intr = in.intrinsics; P.disps_sens = in.disps_sens;
@@ -441,10 +514,11 @@ cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const 
   P.HW = g.HW; P.wd = g.wd; P.S = g.S; P.tiles_per_split = tiles_per_split;
   P.ntiles = (g.HW + 31) / 32;
   P.degmax = degmax;
-  const size_t smem = linearize_tc_smem_bytes(degmax);
+  const size_t smem = linearize_tc_smem_bytes(degmax, wide);
   // inputs that fit the L2 with room to spare stay resident across the LM iterations of a call
   const bool stream = g_tc_stream_mode < 0 ? size_t(g.E) * g.HW * 16 > size_t(100) << 20 : g_tc_stream_mode != 0;
-  auto kern = stream ? k_linearize_tc<true> : k_linearize_tc<false>;
+  auto kern = wide ? (stream ? k_linearize_tc<true, true> : k_linearize_tc<false, true>)
+                   : (stream ? k_linearize_tc<true, false> : k_linearize_tc<false, false>);
   cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (err != cudaSuccess) return err;
   kern<<<nkf * g.S, NT, smem, st>>>(P);
