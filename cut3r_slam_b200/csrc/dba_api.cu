@@ -86,7 +86,8 @@ struct dba_ctx {
   double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // linearize, assemble, allreduce, cholesky, backsub, retract, -, launches
   std::vector<cudaEvent_t> ev;
   cudaStream_t side = nullptr;       // the few high-degree keyframes (SIMT kernel) run beside the tcgen05 launch
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
+  cudaStream_t side2 = nullptr;      // the WIDE tcgen05 keyframes when the SIMT kernel already occupies `side`
   int opt_splits = 0;
   int opt_ppl = 0;
   // plan cache
@@ -100,7 +101,7 @@ struct dba_ctx {
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
   bool opt_tc = true;
-  bool opt_wide_tc = false;          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
+  bool opt_wide_tc = true;           // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
   int64_t* h_idx = nullptr;
@@ -367,19 +368,26 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     if (g.E > 0) {
       const bool fork = g.n_tc > 0 && (g.n_simt > 0 || g.n_wide > 0) && ctx->side != nullptr;
       cudaStream_t s2 = fork ? ctx->side : st;
-      if (fork) {   // long one-per-SM CTAs first (side stream) so that they do not form the tail of the stage
+      // the WIDE launch gets its own stream when the SIMT kernel is on `side`, so that the two run side by side
+      cudaStream_t sw = (fork && g.n_simt > 0 && g.n_wide > 0 && ctx->side2 != nullptr) ? ctx->side2 : s2;
+      if (fork) {   // long one-per-SM CTAs first (side streams) so that they do not form the tail of the stage
         CK(cudaEventRecord(ctx->ev_fork, st), "fork");
         CK(cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0), "fork");
+        if (sw != s2) CK(cudaStreamWaitEvent(sw, ctx->ev_fork, 0), "fork");
       }
       if (fork && g.n_simt > 0)
         CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, s2), "linearize");
       if (fork && g.n_wide > 0)
-        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, true, s2), "linearize (tcgen05, wide)");
-      if (fork) CK(cudaEventRecord(ctx->ev_join, ctx->side), "join");
+        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, true, sw), "linearize (tcgen05, wide)");
+      if (fork) {
+        CK(cudaEventRecord(ctx->ev_join, ctx->side), "join");
+        if (sw != s2) CK(cudaEventRecord(ctx->ev_join2, sw), "join");
+      }
       if (g.n_tc > 0)
         CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, false, st), "linearize (tcgen05)");
       if (fork) {
         CK(cudaStreamWaitEvent(st, ctx->ev_join, 0), "join");
+        if (sw != s2) CK(cudaStreamWaitEvent(st, ctx->ev_join2, 0), "join");
       } else {
         if (g.n_wide > 0)
           CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, true, st), "linearize (tcgen05, wide)");
@@ -478,6 +486,12 @@ dba_ctx* dba_create(int device) {
     if (c->side) cudaStreamDestroy(c->side);
     c->side = nullptr;
   }
+  if (c->side != nullptr &&
+      (cudaStreamCreateWithPriority(&c->side2, cudaStreamNonBlocking, hi_pri) != cudaSuccess ||
+       cudaEventCreateWithFlags(&c->ev_join2, cudaEventDisableTiming) != cudaSuccess)) {
+    if (c->side2) cudaStreamDestroy(c->side2);
+    c->side2 = nullptr;
+  }
   return c;
 }
 
@@ -491,6 +505,8 @@ void dba_destroy(dba_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
+  if (c->side2) cudaStreamDestroy(c->side2);
+  if (c->ev_join2) cudaEventDestroy(c->ev_join2);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->h_idx) cudaFreeHost(c->h_idx);

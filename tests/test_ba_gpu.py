@@ -333,12 +333,12 @@ def test_wide_tensor_core_keyframes():
     poses64, disps64, infos = od.oracle_ba(*p.ba_args(), dtype=torch.float64, return_info=True)
     poses32, disps32, infos32 = od.oracle_ba(*p.ba_args(), dtype=torch.float32, return_info=True)
     gap = rel_err(infos32[0][0], infos[0][0])
-    simt_poses, simt_disps, simt_dx = _run_stepwise(p)
-    db.set_option("wide_tensor_cores", 1)
+    db.set_option("wide_tensor_cores", 0)
     try:
-        poses, disps, dxs = _run_stepwise(p)
+        simt_poses, simt_disps, simt_dx = _run_stepwise(p)
     finally:
-        db.set_option("wide_tensor_cores", 0)
+        db.set_option("wide_tensor_cores", 1)      # the default
+    poses, disps, dxs = _run_stepwise(p)
     assert rel_err(dxs[0], infos[0][0]) < 3 * gap + 1e-5
     assert rel_err(disps, disps64) < 1e-4
     assert rel_err(dxs[0], simt_dx[0]) < 3 * gap + 1e-5
