@@ -101,7 +101,7 @@ struct dba_ctx {
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
   bool opt_tc = true;
-  bool opt_wide_tc = true;           // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
+  int opt_wide_tc = 2;               // 0: SIMT above out-degree 20; 1: WIDE tcgen05 variant up to 25; 2: up to 41          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
   int64_t* h_idx = nullptr;
@@ -244,20 +244,24 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW;
 
   // kernel assignment of the source keyframes
-  std::vector<int32_t> tc_list, simt_list, wide_list;
-  int degmax_wide = 0;
-  const bool use_wide = use_tc && ctx->opt_wide_tc &&
-                        linearize_tc_smem_bytes(linearize_tc_wide_max_degree(), true) <= ctx->smem_cap;
+  std::vector<int32_t> tc_list, simt_list, wide_list, wide2_list;
+  int degmax_wide = 0, degmax_wide2 = 0;
+  const bool use_wide = use_tc && ctx->opt_wide_tc >= 1 &&
+                        linearize_tc_smem_bytes(linearize_tc_wide_max_degree(1), 1) <= ctx->smem_cap;
+  const bool use_wide2 = use_wide && ctx->opt_wide_tc >= 2 &&
+                         linearize_tc_smem_bytes(linearize_tc_wide_max_degree(2), 2) <= ctx->smem_cap;
   for (int m = 0; m < P.M; ++m) {
     const int dgm = P.koff[m + 1] - P.koff[m];
     if (use_tc && dgm <= linearize_tc_max_degree()) tc_list.push_back(m);
-    else if (use_wide && dgm <= linearize_tc_wide_max_degree()) { wide_list.push_back(m); degmax_wide = std::max(degmax_wide, dgm); }
+    else if (use_wide && dgm <= linearize_tc_wide_max_degree(1)) { wide_list.push_back(m); degmax_wide = std::max(degmax_wide, dgm); }
+    else if (use_wide2 && dgm <= linearize_tc_wide_max_degree(2)) { wide2_list.push_back(m); degmax_wide2 = std::max(degmax_wide2, dgm); }
     else simt_list.push_back(m);
   }
   auto by_degree = [&](int32_t a, int32_t b) { return (P.koff[a + 1] - P.koff[a]) > (P.koff[b + 1] - P.koff[b]); };
   std::stable_sort(tc_list.begin(), tc_list.end(), by_degree);       // heavy keyframes are dispatched first
   std::stable_sort(simt_list.begin(), simt_list.end(), by_degree);
   std::stable_sort(wide_list.begin(), wide_list.end(), by_degree);
+  std::stable_sort(wide2_list.begin(), wide2_list.end(), by_degree);
   // non-source frames of [0,t1)
   std::vector<int32_t> nonsrc;
   for (int f = 0; f < t1; ++f) if (P.slot_of_frame[f] < 0) nonsrc.push_back(f);
@@ -272,7 +276,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   };
   size_t o_kx = put(P.kx), o_koff = put(P.koff), o_cedge = put(P.cedge), o_ci = put(P.ci), o_cj = put(P.cj);
   size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
-  size_t o_tc = put(tc_list), o_sl = put(simt_list), o_wl = put(wide_list);
+  size_t o_tc = put(tc_list), o_sl = put(simt_list), o_wl = put(wide_list), o_wl2 = put(wide2_list);
   std::vector<int32_t> blist, heavy;
   // small systems: every block gets its own CTA (8 item lanes); large ones: blocks with <= 8 items share a CTA
   const bool all_heavy = P.nSblk <= 1184;
@@ -303,6 +307,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   g.tc_list = base + o_tc; g.simt_list = base + o_sl; g.n_tc = int(tc_list.size()); g.n_simt = int(simt_list.size());
   g.degmax_tc = degmax_tc;
   g.wide_list = base + o_wl; g.n_wide = int(wide_list.size()); g.degmax_wide = degmax_wide;
+  g.wide2_list = base + o_wl2; g.n_wide2 = int(wide2_list.size()); g.degmax_wide2 = degmax_wide2;
   g.sblk_items = ctx->d_items.as<Item>();
   g.rhs_items = ctx->d_items.as<Item>() + n_s;
   g.nSblk = P.nSblk;
@@ -366,10 +371,10 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   for (int it = 0; it < iterations; ++it) {
     mark();
     if (g.E > 0) {
-      const bool fork = g.n_tc > 0 && (g.n_simt > 0 || g.n_wide > 0) && ctx->side != nullptr;
+      const bool fork = g.n_tc > 0 && (g.n_simt > 0 || g.n_wide > 0 || g.n_wide2 > 0) && ctx->side != nullptr;
       cudaStream_t s2 = fork ? ctx->side : st;
       // the WIDE launch gets its own stream when the SIMT kernel is on `side`, so that the two run side by side
-      cudaStream_t sw = (fork && g.n_simt > 0 && g.n_wide > 0 && ctx->side2 != nullptr) ? ctx->side2 : s2;
+      cudaStream_t sw = (fork && (g.n_simt > 0 || g.n_wide2 > 0) && g.n_wide > 0 && ctx->side2 != nullptr) ? ctx->side2 : s2;
       if (fork) {   // long one-per-SM CTAs first (side streams) so that they do not form the tail of the stage
         CK(cudaEventRecord(ctx->ev_fork, st), "fork");
         CK(cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0), "fork");
@@ -377,20 +382,24 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       }
       if (fork && g.n_simt > 0)
         CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, s2), "linearize");
+      if (fork && g.n_wide2 > 0)
+        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide2_list, g.n_wide2, g.degmax_wide2, 2, s2), "linearize (tcgen05, wide 2)");
       if (fork && g.n_wide > 0)
-        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, true, sw), "linearize (tcgen05, wide)");
+        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, 1, sw), "linearize (tcgen05, wide)");
       if (fork) {
         CK(cudaEventRecord(ctx->ev_join, ctx->side), "join");
         if (sw != s2) CK(cudaEventRecord(ctx->ev_join2, sw), "join");
       }
       if (g.n_tc > 0)
-        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, false, st), "linearize (tcgen05)");
+        CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, 0, st), "linearize (tcgen05)");
       if (fork) {
         CK(cudaStreamWaitEvent(st, ctx->ev_join, 0), "join");
         if (sw != s2) CK(cudaStreamWaitEvent(st, ctx->ev_join2, 0), "join");
       } else {
+        if (g.n_wide2 > 0)
+          CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide2_list, g.n_wide2, g.degmax_wide2, 2, st), "linearize (tcgen05, wide 2)");
         if (g.n_wide > 0)
-          CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, true, st), "linearize (tcgen05, wide)");
+          CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.wide_list, g.n_wide, g.degmax_wide, 1, st), "linearize (tcgen05, wide)");
         if (g.n_simt > 0)
           CK(launch_linearize(g, in, ws, motion_only, ctx->plan_tps, ctx->plan_ppl, g.simt_list, g.n_simt, st), "linearize");
       }
@@ -523,7 +532,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
   else if (n == "tensor_cores") { ctx->opt_tc = value != 0; ctx->plan_valid = false; }
-  else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = value != 0; ctx->plan_valid = false; }
+  else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = int(value); ctx->plan_valid = false; }
   else if (n == "small_system") ctx->opt_small = value != 0;
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }

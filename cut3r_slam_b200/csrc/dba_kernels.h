@@ -18,8 +18,8 @@ struct DeviceGraph {
   const int32_t *kx, *koff, *cedge, *ci, *cj, *pairbase, *blkbase, *nonsrc;
   int n_nonsrc;
   // source-keyframe slots by linearisation kernel: tensor-core Schur products (out-degree <= 20) / SIMT
-  const int32_t *tc_list, *simt_list, *wide_list;   // wide_list: out-degree 21..25 on the WIDE tcgen05 variant
-  int n_tc, n_simt, degmax_tc, n_wide, degmax_wide;
+  const int32_t *tc_list, *simt_list, *wide_list, *wide2_list;   // wide lists: out-degree 21..25 / 26..41 (WIDE variants)
+  int n_tc, n_simt, degmax_tc, n_wide, degmax_wide, n_wide2, degmax_wide2;
   const int32_t *sblk_off, *rhs_off;
   const Item *sblk_items, *rhs_items;
   int nSblk;
@@ -60,9 +60,9 @@ cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Wor
                              int tiles_per_split, int ppl, const int32_t* kf_list, int nkf, cudaStream_t st);
 // tcgen05 variant (dba_linearize_tc.cu): keyframes of kf_list, all with out-degree <= linearize_tc_max_degree()
 cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
-                                const int32_t* kf_list, int nkf, int degmax, bool wide, cudaStream_t st);
-size_t linearize_tc_smem_bytes(int degmax, bool wide = false);
-int linearize_tc_wide_max_degree();
+                                const int32_t* kf_list, int nkf, int degmax, int wide, cudaStream_t st);
+size_t linearize_tc_smem_bytes(int degmax, int wide = 0);
+int linearize_tc_wide_max_degree(int level);
 extern int g_tc_stream_mode;
 int linearize_tc_max_degree();
 int linearize_tc_ppl();

@@ -37,6 +37,9 @@ constexpr int TMEM_COLS = 128;         // one fp32 accumulator, N <= 128 columns
 // D2 = P'[128..255] P'[0..N2)^T (N2 <= 160) in TMEM columns 128.., whose 32 meaningful lanes belong to the
 // warps of lane quarter 0; one CTA per SM (80 more accumulator registers in those warps).
 constexpr int WIDE_MAXDEG = 25;
+// WIDE = 2 (out-degree 26..41, R + 1 <= 253): the second product has all 128 rows and up to 256 columns, every
+// warp holds up to 8 more column groups of its lane quarter (what does not fit 255 registers lives in local memory).
+constexpr int WIDE2_MAXDEG = 41;
 constexpr int TMEM_COLS_WIDE = 512;
 constexpr int D2COL = 128;
 
@@ -131,7 +134,7 @@ __device__ __forceinline__ void tc_load(const float* __restrict__ tg, const floa
   }
 }
 
-template <bool STREAM, bool WIDE>
+template <bool STREAM, int WIDE>
 __global__ void __launch_bounds__(NT, WIDE ? 1 : 2)
 k_linearize_tc(const LinParams P) {
   constexpr uint32_t TILE = WIDE ? TILE_BYTES_256 : TILE_BYTES_128;
@@ -209,7 +212,9 @@ k_linearize_tc(const LinParams P) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) tot[gi][j] = 0.f;
   // WIDE: rows 128 + lane of the second product, column groups g = 2*gi + h (warps 0 and 4 only)
-  constexpr int NG2 = WIDE ? 5 : 1;
+  constexpr int NG2 = WIDE == 2 ? 8 : (WIDE == 1 ? 5 : 1);
+  const bool has2 = WIDE == 2 || (WIDE == 1 && qd == 0);       // warp-uniform: this warp reads the second product
+  const int maxcol2 = 6 * ((128 + 32 * qd + 31) / 6) + 5;
   float tot2[NG2][16];
 #pragma unroll
   for (int gi = 0; gi < NG2; ++gi)
@@ -228,13 +233,13 @@ k_linearize_tc(const LinParams P) {
         for (int j = 0; j < 16; ++j) tot[gi][j] += __uint_as_float(v1[j]);
       }
     }
-    if (WIDE && qd == 0) {
+    if (WIDE && has2) {
 #pragma unroll
       for (int gi = 0; gi < NG2; ++gi) {
         const int g = 2 * gi + h;
-        if (16 * g < N2) {                                        // warp-uniform
+        if (16 * g < N2 && 16 * g <= maxcol2) {                   // warp-uniform
           uint32_t v1[16];
-          tmem_ld16(tmem + D2COL + 16 * g, v1);
+          tmem_ld16(tmem + tlane + D2COL + 16 * g, v1);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) tot2[gi][j] += __uint_as_float(v1[j]);
@@ -464,8 +469,8 @@ k_linearize_tc(const LinParams P) {
       }
     }
   }
-  if (WIDE && qd == 0) {
-    const int row2 = 128 + lane;
+  if (WIDE && has2) {
+    const int row2 = 128 + 32 * qd + lane;
     const int A = row2 / 6, ri = row2 - A * 6;
     float* Sdst = P.Spart + slab0 + int64_t(A) * (A + 1) / 2 * 36 + ri * 6;
 #pragma unroll
@@ -495,15 +500,15 @@ k_linearize_tc(const LinParams P) {
 
 int g_tc_stream_mode = -1;   // -1 auto, 0 L2-resident loads, 1 evict-first loads ("stream_inputs" option)
 
-size_t linearize_tc_smem_bytes(int degmax, bool wide) {
+size_t linearize_tc_smem_bytes(int degmax, int wide) {
   return 2 * KB * (wide ? TILE_BYTES_256 : TILE_BYTES_128) + tc_float_region(degmax) * sizeof(float) + 32;
 }
 int linearize_tc_max_degree() { return 20; }
-int linearize_tc_wide_max_degree() { return WIDE_MAXDEG; }
+int linearize_tc_wide_max_degree(int level) { return level == 2 ? WIDE2_MAXDEG : WIDE_MAXDEG; }
 int linearize_tc_ppl() { return PPL; }
 
 cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
-                                const int32_t* kf_list, int nkf, int degmax, bool wide, cudaStream_t st) {
+                                const int32_t* kf_list, int nkf, int degmax, int wide, cudaStream_t st) {
   if (nkf == 0) return cudaSuccess;
   LinParams P;
   P.poses = in.poses; P.disps = in.disps; P.intr = in.intrinsics; P.disps_sens = in.disps_sens;
@@ -517,8 +522,9 @@ cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const 
   const size_t smem = linearize_tc_smem_bytes(degmax, wide);
   // inputs that fit the L2 with room to spare stay resident across the LM iterations of a call
   const bool stream = g_tc_stream_mode < 0 ? size_t(g.E) * g.HW * 16 > size_t(100) << 20 : g_tc_stream_mode != 0;
-  auto kern = wide ? (stream ? k_linearize_tc<true, true> : k_linearize_tc<false, true>)
-                   : (stream ? k_linearize_tc<true, false> : k_linearize_tc<false, false>);
+  auto kern = wide == 2 ? (stream ? k_linearize_tc<true, 2> : k_linearize_tc<false, 2>)
+            : wide == 1 ? (stream ? k_linearize_tc<true, 1> : k_linearize_tc<false, 1>)
+                        : (stream ? k_linearize_tc<true, 0> : k_linearize_tc<false, 0>);
   cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (err != cudaSuccess) return err;
   kern<<<nkf * g.S, NT, smem, st>>>(P);
