@@ -34,7 +34,9 @@ const char* dba_version(void);
  * "splits" n -- CTAs per source keyframe (0 = auto); "keep_system" 0/1 -- keep a copy of the reduced
  * system of the last iteration for dba_debug_read; "ppl" n -- pixels per lane override (0 = auto);
  * "profile" 0/1 -- bracket every stage with CUDA events on `stream` and accumulate per-stage times
- * (setting it resets the accumulators; the call then waits for its last event before returning). */
+ * (setting it resets the accumulators; the call then waits for its last event before returning);
+ * "tensor_cores" 0/1 -- Schur products on tcgen05 (default 1); "wide_tensor_cores" 0/1/2 -- keyframes with
+ * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
 
 /* ---- ba: replaces droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
