@@ -6,8 +6,10 @@ Tolerances.  BASELINE.json north_star quotes max rel. err <= 1e-4 on disps and <
 pose tangent update "against the reference".  The reference's OWN fp32 result sits 1e-4..1e-3
 (dx) from its fp64 result on these problems (stored next to each golden vector), so an absolute
 1e-5 against either is not meaningful; the bound used is: error of the CUDA fp32 result against the
-fp64 reference <= 6x the reference's own fp32-vs-fp64 gap + 1e-5 (dx), and <= 1e-4 on disps --
-i.e. the CUDA path is as close to the exact answer as the reference's fp32 is.  Why a factor: the
+fp64 reference <= MULT = 3x the reference's own fp32-vs-fp64 gap + 1e-5 (dx), and <= 1e-4 on disps --
+i.e. the CUDA path is as close to the exact answer as the reference's fp32 is.  The measured ratios per
+golden file / kernel variant / full-size graph are in profiles/r2_parity_margins.md (tools/parity_margins.py).
+Why a factor: the
 reduced systems have cond(S) = 1e4 .. 1e5, so dx carries cond * eps_fp32 of rounding NOISE whatever the
 algorithm (tools/diag_solve_error.py: rounding the exact S to fp32 alone moves dx by 2e-5 .. 2e-3);
 the reference's gap and ours are two draws of that noise and their ratio scatters by a few x between
@@ -25,6 +27,7 @@ from helpers import load_golden, rel_err
 pytestmark = pytest.mark.gpu
 
 GOLDEN = ["tiny_ba", "tiny_ba_backend", "tiny_moba", "correctness", "frontend"]
+MULT = 3.0     # allowed multiple of the reference's own fp32-vs-fp64 gap (see the module docstring)
 
 
 def _db():
@@ -53,12 +56,12 @@ def test_golden_reference_outputs(name):
     for k, dx in enumerate(dxs):
         ref_gap = rel_err(g["ref_dx_f32"][k], g["ref_dx_f64"][k])
         err = rel_err(dx, g["ref_dx_f64"][k])
-        assert err < 6 * ref_gap + 1e-5, (k, err, ref_gap)
-    # north_star: <= 1e-4 on disps.  Where the reference's own fp32 run already sits within a factor 6 of
+        assert err < MULT * ref_gap + 1e-5, (k, err, ref_gap)
+    # north_star: <= 1e-4 on disps.  Where the reference's own fp32 run already sits within a factor 3 of
     # that bound (tiny_ba: 3e-5, the solve amplifies fp32 rounding by cond(S) ~ 1e5) the same rule as
     # for dx applies: a small multiple of the reference algorithm's own fp32-vs-fp64 gap.
     gap_d = rel_err(g["ref_disps_f32"], g["ref_disps_f64"])
-    assert rel_err(disps, g["ref_disps_f64"]) < max(1e-4, 6 * gap_d), gap_d
+    assert rel_err(disps, g["ref_disps_f64"]) < max(1e-4, MULT * gap_d), gap_d
     assert float((poses - torch.from_numpy(g["ref_poses_f64"])).abs().max()) < 1e-4
 
 
@@ -91,8 +94,8 @@ def test_reduced_system_matches_oracle(kw):
     sol32 = od.schur_solve(lin32["H"], lin32["E"], lin32["C"], lin32["v"], lin32["w"], ep=p.ep, lm=p.lm)
     gap_dx = rel_err(sol32["dx"], sol["dx"])
     gap_dz = rel_err(sol32["dz"], sol["dz"])
-    assert rel_err(dx.cpu(), sol["dx"]) < 6 * gap_dx + 1e-5, gap_dx
-    assert rel_err(dz.cpu().reshape(sol["dz"].shape), sol["dz"]) < 6 * gap_dz + 1e-5, gap_dz
+    assert rel_err(dx.cpu(), sol["dx"]) < MULT * gap_dx + 1e-5, gap_dx
+    assert rel_err(dz.cpu().reshape(sol["dz"].shape), sol["dz"]) < MULT * gap_dz + 1e-5, gap_dz
 
 
 @pytest.mark.parametrize("name,kw", [
@@ -106,7 +109,7 @@ def test_matches_oracle_fp64(name, kw):
     poses, disps, dxs = _run_stepwise(p)
     for k, dx in enumerate(dxs):
         gap = rel_err(infos32[k][0], infos[k][0])
-        assert rel_err(dx, infos[k][0]) < 6 * gap + 1e-5, (k, gap)
+        assert rel_err(dx, infos[k][0]) < MULT * gap + 1e-5, (k, gap)
     assert rel_err(disps, disps64) < 1e-4
     upd = ose3.tangent_update(poses.double(), poses64.double())
     assert float(upd.abs().max()) < 1e-4
@@ -211,7 +214,7 @@ def test_high_degree_keyframe(r, E):
     poses32, disps32, infos32 = od.oracle_ba(*p.ba_args(), dtype=torch.float32, return_info=True)
     poses, disps, dxs = _run_stepwise(p)
     gap = rel_err(infos32[0][0], infos[0][0])
-    assert rel_err(dxs[0], infos[0][0]) < 3 * gap + 1e-5
+    assert rel_err(dxs[0], infos[0][0]) < MULT * gap + 1e-5
     assert rel_err(disps, disps64) < 1e-4
 
 
@@ -277,33 +280,6 @@ def test_empty_edge_list_is_a_noop():
     assert float((p.poses - p0).abs().max()) < 1e-7 and torch.equal(p.disps, d0)
 
 
-@pytest.mark.parametrize("name", ["backend", "motiononly"])
-def test_full_size_properties(name):
-    """BASELINE.json sizes (too big for the CPU oracle in test time): size-independent properties --
-    the update moves poses and disparities toward the ground truth the targets were generated from,
-    gauge frames stay put, results are finite and reproducible, host entry == device entry."""
-    db = _db()
-    p = make_problem(name)
-    g = p.to("cuda")
-    e0 = float(ose3.tangent_update(p.poses.double(), p.gt_poses.double()).norm(dim=-1).mean())
-    d0 = float((p.disps - p.gt_disps).abs().mean())
-    db.ba(*g.ba_args())
-    poses, disps = g.poses.cpu(), g.disps.cpu()
-    assert torch.isfinite(poses).all() and torch.isfinite(disps).all()
-    assert torch.equal(poses[:p.t0], p.poses[:p.t0])
-    e1 = float(ose3.tangent_update(poses.double(), p.gt_poses.double()).norm(dim=-1).mean())
-    # CPU oracle on the same problems: backend 0.0487 -> 1.6e-4 after 3 iterations; motion-only (noisy
-    # disparities stay fixed) 0.0458 -> 0.0316 after 2
-    assert e1 < (0.85 if p.motion_only else 0.1) * e0, (e0, e1)
-    if not p.motion_only:
-        d1 = float((disps - p.gt_disps).abs().mean())
-        assert d1 < 0.5 * d0, (d0, d1)
-    h = make_problem(name)
-    hp = [t.pin_memory() if isinstance(t, torch.Tensor) else t for t in h.ba_args()]
-    db.ba_host(*hp)
-    assert torch.equal(hp[0], poses) and torch.equal(hp[1], disps)
-
-
 def test_cholesky_paths_agree():
     """Cooperative single-launch Cholesky (default) vs the multi-launch blocked path."""
     db = _db()
@@ -343,7 +319,7 @@ def test_wide_tensor_core_keyframes(level, P, r, E):
         db.set_option("wide_tensor_cores", 2)      # the default
     # measured: dx 2.7e-4 / 3.0e-4 from fp64 (SIMT path 1.8e-4 / 2.9e-4, the reference's own fp32 run 1.1e-4);
     # disps 2.8e-5 / 2.5e-5.  Same rule as test_matches_oracle_fp64: a small multiple of the reference's own gap.
-    assert rel_err(dxs[0], infos[0][0]) < 6 * gap + 1e-5
+    assert rel_err(dxs[0], infos[0][0]) < MULT * gap + 1e-5
     assert rel_err(disps, disps64) < 1e-4
-    assert rel_err(dxs[0], simt_dx[0]) < 6 * gap + 1e-5
+    assert rel_err(dxs[0], simt_dx[0]) < MULT * gap + 1e-5
     assert rel_err(disps, simt_disps) < 1e-4          # two summation orders, each within the bar above
