@@ -157,51 +157,51 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=WORKLOAD)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--opt", action="append", default=[], help="libdba option name=value (developer experiments)")
-    ap.add_argument("--brief", action="store_true", help="print only ms/step and the per-stage times")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3)
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        run_reference(args, rank)
-        return
-
+def sharded_parity(db, sh, p, world, rank, dev, shards):
+    """Correctness signal for the N > 1 lines (outside any timed region): the sharded call against the same `ba`
+    on one GPU (rank 0, whole graph), and whether the replicated poses are bit-identical on every rank."""
     import torch.distributed as dist
-    from cut3r_slam_b200 import droid_backends as db
-    from cut3r_slam_b200.sharded import ShardedBA, partition_by_source
+    single = None
+    if rank == 0:
+        s = p.to(dev)
+        db.ba(*s.ba_args())
+        torch.cuda.synchronize()
+        single = (s.poses.clone(), s.disps.clone())
+        del s
+    g = p.to(dev)
+    mine = shards[rank]
+    sel = mine["edges"].to(dev)
+    lo, hi = mine["slots"]
+    sh.ba(g.poses, g.disps, g.intrinsics, None, g.targets[sel].contiguous(), g.weights[sel].contiguous(),
+          g.eta[lo:hi].contiguous(), g.ii[sel].contiguous(), g.jj[sel].contiguous(), p.t0, p.t1, p.iterations, p.lm, p.ep)
+    sh.gather_disps(g.disps, shards)
+    torch.cuda.synchronize()
+    ref = g.poses.clone()
+    dist.broadcast(ref, src=0)
+    same = torch.tensor([int(torch.equal(ref, g.poses))], device=dev)
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    out = None
+    if rank == 0:
+        sp, sd = single
+        out = {"max_abs_poses_vs_1gpu": float((sp - g.poses).abs().max()),
+               "disps_rel_vs_1gpu": float((sd - g.disps).abs().max() / sd.abs().max()),
+               "poses_identical_across_ranks": bool(same.item())}
+    dist.barrier()
+    return out
+
+
+def run_workload(name, args, db, sh, world, rank, dev, steps, warmup, flush, full):
+    """Times one workload; returns the dict of measurements (rank 0) -- `full` adds e2e / cold-plan / parity."""
+    import torch.distributed as dist
+    from cut3r_slam_b200.sharded import partition_by_source
     from cut3r_slam_b200.synthetic import CONFIGS, make_problem
-
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-
-    for o in args.opt:
-        k_, v_ = o.split("=")
-        db.set_option(k_, float(v_), dev)
-    cfg = CONFIGS[args.workload]
-    p = make_problem(args.workload)
+    cfg = CONFIGS[name]
+    p = make_problem(name)
     E, HW, Pp = p.ii.numel(), p.disps.shape[1] * p.disps.shape[2], p.t1 - p.t0
     M = int(torch.unique(p.ii).numel())
     iters = p.iterations
-
-    # ---- shard (N > 1) or take the whole graph -------------------------------------------------
-    sh = ShardedBA(dev)
+    shards = None
     if world > 1:
-        sh.init_comm()
         shards = partition_by_source(p.ii, world)
         mine = shards[rank]
         sel = mine["edges"]
@@ -218,25 +218,27 @@ def main():
     poses, disps = poses0.clone(), disps0.clone()
     intr, targets, weights, eta = h_intr.to(dev), h_targets.to(dev), h_weights.to(dev), h_eta.to(dev)
     ii, jj = h_ii.to(dev), h_jj.to(dev)
-    sens = None
-    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)    # > 126 MB L2
 
     def step_device():
         poses.copy_(poses0)
         disps.copy_(disps0)
-        db.ba(poses, disps, intr, sens, targets, weights, eta, ii, jj, p.t0, p.t1, iters, p.lm, p.ep, p.motion_only)
+        if world > 1:       # the step ends with complete disparities on every rank
+            sh.ba(poses, disps, intr, None, targets, weights, eta, ii, jj, p.t0, p.t1, iters, p.lm, p.ep)
+            sh.gather_disps(disps, shards)
+        else:
+            db.ba(poses, disps, intr, None, targets, weights, eta, ii, jj, p.t0, p.t1, iters, p.lm, p.ep, p.motion_only)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
+    def timed(fn, nsteps, nwarm):
+        for _ in range(nwarm):
             flush.fill_(1.0)
             fn()
         barrier()
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nsteps)]
         launches = 0
         for a, b in evs:
             flush.fill_(1.0)                   # L2 flush between timed steps (outside the event pair)
@@ -245,49 +247,123 @@ def main():
             a.record()
             fn()
             b.record()
-            launches += db.last_launch_count()
+            launches += sh.last_launch_count() if world > 1 else db.last_launch_count()
         barrier()
         ms = sum(a.elapsed_time(b) for a, b in evs)
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()) / steps, launches
+        return float(t.item()) / nsteps, launches
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(dev.index)
     sampler.start()
-    ms_step, launches = timed(step_device, args.steps, args.warmup)
+    ms_step, launches = timed(step_device, steps, warmup)
     clocks = sampler.stop()
+    out = {"name": name, "cfg": cfg, "p": p, "E": E, "HW": HW, "M": M, "Pp": Pp, "iters": iters, "ms_step": ms_step,
+           "launches": launches, "clocks": clocks, "E_loc": int(sel.numel()), "M_loc": hi - lo}
 
     # ---- end to end: pinned host buffers in, poses + disps out, through dba_ba_host ------------------
-    w_poses, w_disps = h_poses.clone().pin_memory(), h_disps.clone().pin_memory()
+    if full:
+        w_poses, w_disps = h_poses.clone().pin_memory(), h_disps.clone().pin_memory()
+        ctx = sh.ctx if world > 1 else None
 
-    def step_host():
-        w_poses.copy_(h_poses)
-        w_disps.copy_(h_disps)
-        db.ba_host(w_poses, w_disps, h_intr, None, h_targets, h_weights, h_eta, h_ii, h_jj, p.t0, p.t1, iters, p.lm,
-                   p.ep, p.motion_only, device=dev)
+        def step_host():
+            w_poses.copy_(h_poses)
+            w_disps.copy_(h_disps)
+            db.ba_host(w_poses, w_disps, h_intr, None, h_targets, h_weights, h_eta, h_ii, h_jj, p.t0, p.t1, iters,
+                       p.lm, p.ep, p.motion_only, device=dev, _ctx=ctx)
 
-    e2e_steps = max(3, min(args.steps, 10))
-    ms_e2e, _ = timed(step_host, e2e_steps, 3)
-    h2d = sum(t.numel() * t.element_size() for t in (h_poses, h_disps, h_intr, h_targets, h_weights, h_eta))
-    d2h = sum(t.numel() * t.element_size() for t in (h_poses, h_disps)) + Pp * 6 * 4
+        out["ms_e2e"], _ = timed(step_host, max(3, min(steps, 10)), 3)
+        out["h2d"] = sum(t.numel() * t.element_size() for t in (h_poses, h_disps, h_intr, h_targets, h_weights, h_eta))
+        out["d2h"] = sum(t.numel() * t.element_size() for t in (h_poses, h_disps)) + Pp * 6 * 4
+
+    # ---- cold plan: the edge list changes on every call (a real SLAM loop edits the graph between updates), so
+    # each call copies ii / jj to the host, rebuilds the plan (CSR + gather lists) and uploads it
+    if full and world == 1:
+        perm = torch.randperm(E, generator=torch.Generator().manual_seed(7))
+        alt = [(ii, jj, targets, weights), (ii[perm.to(dev)].contiguous(), jj[perm.to(dev)].contiguous(),
+                                            targets[perm.to(dev)].contiguous(), weights[perm.to(dev)].contiguous())]
+        flip = [0]
+
+        def step_cold():
+            poses.copy_(poses0)
+            disps.copy_(disps0)
+            a = alt[flip[0] & 1]
+            flip[0] += 1
+            db.ba(poses, disps, intr, None, a[2], a[3], eta, a[0].clone(), a[1].clone(), p.t0, p.t1, iters, p.lm, p.ep,
+                  p.motion_only)
+
+        out["ms_cold"], _ = timed(step_cold, max(3, min(steps, 6)), 2)
+        del alt
 
     # ---- per-stage device times (CUDA events inside libdba, on the launching stream) ------------
-    db.set_option("profile", 1, dev)
-    prof_steps = max(3, min(args.steps, 10))
-    timed(step_device, prof_steps, 1)
-    stages, n_it = db.stage_times(dev)
-    db.set_option("profile", 0, dev)
-    stage_ms = {k: v / max(n_it, 1) for k, v in stages.items()}          # per LM iteration
-    stage_all = None
+    setopt = (lambda k, v: sh.ctx.set_option(k, v)) if world > 1 else (lambda k, v: db.set_option(k, v, dev))
+    setopt("profile", 1)
+    timed(step_device, max(3, min(steps, 10)), 1)
+    stages, n_it = sh.stage_times() if world > 1 else db.stage_times(dev)
+    setopt("profile", 0)
+    out["stage_ms"] = {k: v / max(n_it, 1) for k, v in stages.items()}          # per LM iteration
+    out["stage_all"] = None
     if world > 1:                                                         # every rank's stage times (diagnosis of skew)
-        keys = sorted(stage_ms)
-        mine_t = torch.tensor([stage_ms[k] for k in keys], dtype=torch.float64, device=dev)
+        keys = sorted(out["stage_ms"])
+        mine_t = torch.tensor([out["stage_ms"][k] for k in keys], dtype=torch.float64, device=dev)
         allt = [torch.zeros_like(mine_t) for _ in range(world)]
         dist.all_gather(allt, mine_t)
-        stage_all = {k: [round(float(t[i]) * 1e3, 1) for t in allt] for i, k in enumerate(keys)}
-    E_loc = int(sel.numel())
-    lin_bytes = linearize_bytes(E_loc, HW, hi - lo)
+        out["stage_all"] = {k: [round(float(t[i]) * 1e3, 1) for t in allt] for i, k in enumerate(keys)}
+        out["sharded_parity"] = sharded_parity(db, sh, p, world, rank, dev, shards)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-loopclosure", action="store_true", help="skip the secondary loop-closure object")
+    ap.add_argument("--opt", action="append", default=[], help="libdba option name=value (developer experiments)")
+    ap.add_argument("--brief", action="store_true", help="print only ms/step and the per-stage times")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch.distributed as dist
+    from cut3r_slam_b200 import droid_backends as db
+    from cut3r_slam_b200.sharded import ShardedBA
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    sh = ShardedBA(dev)
+    if world > 1:
+        sh.init_comm()
+    for o in args.opt:
+        k_, v_ = o.split("=")
+        db.set_option(k_, float(v_), dev)
+        sh.ctx.set_option(k_, float(v_))
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)    # > 126 MB L2
+
+    r = run_workload(args.workload, args, db, sh, world, rank, dev, args.steps, args.warmup, flush, full=not args.brief)
+    lc = None
+    if not args.brief and not args.no_loopclosure and args.workload != "loopclosure":
+        # BASELINE.json configs[3] (512 keyframes, 12k edges): the configuration where sharding pays; fewer steps
+        lc = run_workload("loopclosure", args, db, sh, world, rank, dev, max(3, min(args.steps, 5)), 3, flush, full=False)
+
+    p, cfg, E, HW, M, Pp, iters = r["p"], r["cfg"], r["E"], r["HW"], r["M"], r["Pp"], r["iters"]
+    ms_step, stage_ms = r["ms_step"], r["stage_ms"]
+    lin_bytes = linearize_bytes(r["E_loc"], HW, r["M_loc"])
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -301,32 +377,51 @@ def main():
     whole = b_alg * iters / (ms_step * 1e-3) / 1e9
 
     if rank == 0 and args.brief:
-        print(json.dumps({"opts": args.opt, "ms_per_step": round(ms_step, 4), "ms_e2e": round(ms_e2e, 4),
+        print(json.dumps({"opts": args.opt, "ms_per_step": round(ms_step, 4),
                           "stage_us": {k: round(v * 1e3, 1) for k, v in stage_ms.items()},
-                          "stage_us_per_rank": stage_all}), flush=True)
+                          "stage_us_per_rank": r["stage_all"]}), flush=True)
     elif rank == 0:
         ep_per_s = E * HW * iters / (ms_step * 1e-3)
+        ms_e2e = r["ms_e2e"]
         line = {
             "metric": "ba_edge_pixels_per_s", "value": ep_per_s, "unit": "edge-pixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_string(args.workload, cfg, p),
-                       "parallelism": f"edges sharded by source keyframe over {world} GPU(s)" if world > 1 else "1 GPU",
+                       "parallelism": f"edges sharded by source keyframe over {world} GPU(s); the step ends with the "
+                                      f"disparities gathered on every rank" if world > 1 else "1 GPU",
                        "l2": "256 MB buffer written between timed steps (inputs 106 MB < 126 MB L2)"},
             "ba_iters_per_s": iters / (ms_step * 1e-3),
-            "clocks": clocks,
+            "clocks": r["clocks"],
             "e2e": {"value": E * HW * iters / (ms_e2e * 1e-3), "unit": "edge-pixels/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "entry": "dba_ba_host (C ABI, pinned host buffers)"},
-            "gpu_launches": launches,
+                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "entry": "dba_ba_host (C ABI, pinned host buffers)"},
+            "gpu_launches": r["launches"],
             "roofline": {"bound": "hbm", "kernel": "k_linearize (residual/Jacobian/Hessian + Schur, fused)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": lin_bytes,
                          "ms_per_launch": lin_ms, "traffic": measured_traffic(args.workload, world),
+                         "limiter": "instruction issue, not DRAM (ncu, profiles/): the kernel's bytes are HBM-type "
+                                    "work by SURVEY 8(d), its measured bound is the SIMT front end",
                          "whole_iteration": {"algorithmic_bytes": b_alg, "achieved": whole, "frac": whole / peak,
                                              "frac_of_8TBs_nominal": whole / 8000.0}},
             "stage_ms_per_lm_iteration": stage_ms,
-            "stage_us_per_rank": stage_all,
+            "stage_us_per_rank": r["stage_all"],
         }
+        if "ms_cold" in r:
+            line["cold_plan"] = {"ms_per_step": r["ms_cold"],
+                                 "what": "every call sees a NEW edge list: ii/jj to the host (one sync), plan rebuild, upload"}
+        if r.get("sharded_parity") is not None:
+            line["sharded_parity"] = r["sharded_parity"]
+        if lc is not None:
+            lp = lc["p"]
+            line["loopclosure"] = {
+                "workload": workload_string("loopclosure", lc["cfg"], lp), "ms_per_step": lc["ms_step"],
+                "value": lc["E"] * lc["HW"] * lc["iters"] / (lc["ms_step"] * 1e-3), "unit": "edge-pixels/s",
+                "steps": max(3, min(args.steps, 5)), "gpu_launches": lc["launches"],
+                "stage_ms_per_lm_iteration": lc["stage_ms"], "stage_us_per_rank": lc["stage_all"],
+                "sharded_parity": lc.get("sharded_parity"),
+                "l2": "inputs 590 MB > 126 MB L2"}
         if not args.no_cpu_baseline and world == 1:
             import oracle.dba as od
             cores = os.cpu_count() or 1

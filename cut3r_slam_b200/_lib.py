@@ -23,6 +23,9 @@ SIGNATURES = {
     "dba_ba": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
                          C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, c_f, c_f,
                          C.c_void_p]),
+    "dba_ba_cached": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
+                                C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, c_f, c_f,
+                                C.c_void_p, C.c_uint64, c_i, c_i]),
     "dba_ba_host": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
                               C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, c_f, c_f,
                               C.c_void_p]),

@@ -93,7 +93,8 @@ struct dba_ctx {
   // plan cache
   Plan plan;
   bool plan_valid = false;
-  int plan_ppl = 0, plan_tps = 1, plan_HW = 0;
+  int plan_ppl = 0, plan_tps = 1, plan_HW = 0, plan_ht = 0, plan_wd = 0;
+  uint64_t plan_key = 0;             // caller's identity of the edge lists the plan was built from (0: none)
   DevBuf d_plan_i32, d_items;
   DeviceGraph g{};
   // workspace
@@ -144,13 +145,21 @@ int out_degree_max(const int64_t* ii, int64_t E, int N, int* M_out) {
   return mx;
 }
 
+// plan-cache hit by the caller's graph key alone: no look at the edge lists (they may still be on the device)
+bool plan_hit_by_key(dba_ctx* ctx, uint64_t key, int64_t E, int N, int ht, int wd, int64_t M, int t0, int t1,
+                     bool motion_only) {
+  const Plan& P = ctx->plan;
+  return key != 0 && ctx->plan_valid && ctx->plan_key == key && P.E == E && P.N == N && P.t0 == t0 && P.t1 == t1 &&
+         P.motion_only == motion_only && ctx->plan_ht == ht && ctx->plan_wd == wd && (motion_only || M < 0 || M == P.M);
+}
+
 // (re)build the plan for this graph if it differs from the cached one, upload it
 int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, int N, int ht, int wd, int64_t M,
                  int t0, int t1, bool motion_only, cudaStream_t st) {
   const int HW = ht * wd;
   Plan& P = ctx->plan;
   bool same = ctx->plan_valid && P.E == E && P.N == N && P.t0 == t0 && P.t1 == t1 && P.motion_only == motion_only &&
-              ctx->plan_HW == HW && int64_t(P.key_ii.size()) == E &&
+              ctx->plan_ht == ht && ctx->plan_wd == wd && int64_t(P.key_ii.size()) == E &&
               (E == 0 || (std::memcmp(P.key_ii.data(), ii, E * sizeof(int64_t)) == 0 &&
                           std::memcmp(P.key_jj.data(), jj, E * sizeof(int64_t)) == 0));
   if (same) {
@@ -241,7 +250,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   const int tps = (ntilesT + S - 1) / S;
   S = (ntilesT + tps - 1) / tps;     // no empty split
   if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
-  ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW;
+  ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW; ctx->plan_ht = ht; ctx->plan_wd = wd;
 
   // kernel assignment of the source keyframes
   std::vector<int32_t> tc_list, simt_list, wide_list, wide2_list;
@@ -347,10 +356,16 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
 int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const float* disps_sens,
            const float* targets, const float* weights, const float* eta, const int64_t* ii_h, const int64_t* jj_h,
            int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
-           bool motion_only, float* dx_out, float* dz_out, cudaStream_t st, float* cov_out = nullptr) {
+           bool motion_only, float* dx_out, float* dz_out, cudaStream_t st, float* cov_out = nullptr,
+           uint64_t graph_key = 0) {
   g_launch_count = 0;
-  int rc = prepare_plan(ctx, ii_h, jj_h, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only, st);
-  if (rc) return rc;
+  int rc = 0;
+  // ii_h == nullptr: the caller's graph key matched the cached plan (plan_hit_by_key), nothing to look at
+  if (ii_h != nullptr || E == 0) {
+    rc = prepare_plan(ctx, ii_h, jj_h, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only, st);
+    if (rc) return rc;
+    ctx->plan_key = graph_key;
+  }
   Workspace ws{};
   rc = ensure_workspace(ctx, ws);
   if (rc) return rc;
@@ -544,16 +559,8 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   return 0;
 }
 
-int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
-           const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
-           int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
-           int motion_only, float* dx_out, float* dz_out, void* stream) {
-  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, iterations,
-                        motion_only);
-  if (rc) return rc;
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
-  // edge lists -> host (pinned staging), one synchronisation per call
+// device edge lists -> pinned host staging (one synchronisation of `st`)
+static int fetch_edge_lists(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, cudaStream_t st) {
   if (size_t(2 * E) > ctx->h_idx_cap) {
     if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
     ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
@@ -565,8 +572,39 @@ int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, co
     CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
     CK(cudaStreamSynchronize(st), "ii/jj -> host");
   }
-  return run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ctx->h_idx, ctx->h_idx + E, E, N, ht,
-                wd, M, t0, t1, iterations, lm, ep, motion_only != 0, dx_out, dz_out, st);
+  return 0;
+}
+
+int dba_ba_cached(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                  const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                  int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+                  int motion_only, float* dx_out, float* dz_out, void* stream, uint64_t graph_key,
+                  const int64_t* ii_host, const int64_t* jj_host) {
+  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, iterations,
+                        motion_only);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  const int64_t* ih = nullptr;
+  const int64_t* jh = nullptr;
+  if (E > 0 && !plan_hit_by_key(ctx, graph_key, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only != 0)) {
+    if (ii_host != nullptr && jj_host != nullptr) { ih = ii_host; jh = jj_host; }
+    else {
+      rc = fetch_edge_lists(ctx, ii, jj, E, st);      // the only host synchronisation of the call
+      if (rc) return rc;
+      ih = ctx->h_idx; jh = ctx->h_idx + E;
+    }
+  }
+  return run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ih, jh, E, N, ht, wd, M, t0, t1,
+                iterations, lm, ep, motion_only != 0, dx_out, dz_out, st, nullptr, graph_key);
+}
+
+int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+           const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+           int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+           int motion_only, float* dx_out, float* dz_out, void* stream) {
+  return dba_ba_cached(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, E, N, ht, wd, M, t0,
+                       t1, iterations, lm, ep, motion_only, dx_out, dz_out, stream, 0, nullptr, nullptr);
 }
 
 int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* disps_sens,
@@ -578,15 +616,8 @@ int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const fl
   if (E <= 0 || !dzcov_out) return fail_arg(ctx, "depth covariance needs edges and an output buffer");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   CK(cudaSetDevice(ctx->device), "cudaSetDevice");
-  if (size_t(2 * E) > ctx->h_idx_cap) {
-    if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
-    ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
-    CK(cudaMallocHost(&ctx->h_idx, size_t(2 * E + 64) * sizeof(int64_t)), "pinned staging");
-    ctx->h_idx_cap = size_t(2 * E + 64);
-  }
-  CK(cudaMemcpyAsync(ctx->h_idx, ii, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "ii -> host");
-  CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
-  CK(cudaStreamSynchronize(st), "ii/jj -> host");
+  rc = fetch_edge_lists(ctx, ii, jj, E, st);
+  if (rc) return rc;
   // the state is read-only on this path (run_ba's cov branch leaves before any retraction)
   return run_ba(ctx, const_cast<float*>(poses), const_cast<float*>(disps), intrinsics, disps_sens, targets, weights, eta,
                 ctx->h_idx, ctx->h_idx + E, E, N, ht, wd, M, t0, t1, 1, lm, ep, false, nullptr, nullptr, st, dzcov_out);
@@ -681,15 +712,7 @@ static int proj_trans_run(dba_ctx* ctx, const float* poses, const float* disps, 
                           const float* targets, const float* weights, const int64_t* ii, const int64_t* jj, int64_t E,
                           int64_t N, int ht, int wd, int64_t M, float* C_out, float* w_out, cudaStream_t st,
                           const int32_t** kx_out) {
-  if (size_t(2 * E) > ctx->h_idx_cap) {
-    if (ctx->h_idx) cudaFreeHost(ctx->h_idx);
-    ctx->h_idx = nullptr; ctx->h_idx_cap = 0;
-    CK(cudaMallocHost(&ctx->h_idx, size_t(2 * E + 64) * sizeof(int64_t)), "pinned staging");
-    ctx->h_idx_cap = size_t(2 * E + 64);
-  }
-  CK(cudaMemcpyAsync(ctx->h_idx, ii, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "ii -> host");
-  CK(cudaMemcpyAsync(ctx->h_idx + E, jj, E * sizeof(int64_t), cudaMemcpyDeviceToHost, st), "jj -> host");
-  CK(cudaStreamSynchronize(st), "ii/jj -> host");
+  { const int rcf = fetch_edge_lists(ctx, ii, jj, E, st); if (rcf) return rcf; }
   const int64_t* hi = ctx->h_idx; const int64_t* hj = ctx->h_idx + E;
   const bool same = int64_t(ctx->pt_ii.size()) == E && ctx->pt_N == int(N) &&
                     std::memcmp(ctx->pt_ii.data(), hi, E * sizeof(int64_t)) == 0 &&

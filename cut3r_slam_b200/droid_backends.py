@@ -113,7 +113,29 @@ def _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
     return N, ht, wd, E, M
 
 
-def ba(*args):
+_graph_keys = {}      # (ii ptr, ii version, jj ptr, jj version, E, device) -> (key, ii, jj): the tensors are kept alive
+_next_graph_key = [1]
+
+
+def _graph_key(ii, jj):
+    """Identity of the edge lists for libdba's plan cache (dba_ba_cached): FactorGraph keeps `ii` / `jj` as tensors
+    that are REPLACED (torch.cat, boolean indexing: hislam2/factor_graph.py:79-90) when the graph changes and passed
+    unchanged to every `ba` call in between, so (storage address, version counter) identifies the content as long as
+    the tensors are alive -- the cache holds a reference to them, their storage cannot be recycled for another list.
+    A hit means libdba neither copies the lists to the host nor synchronises the stream."""
+    k = (ii.data_ptr(), ii._version, jj.data_ptr(), jj._version, ii.numel(), ii.device.index)
+    hit = _graph_keys.get(k)
+    if hit is not None and hit[1] is ii and hit[2] is jj:
+        return hit[0]
+    if len(_graph_keys) >= 16:                       # small LRU: drop the oldest entry
+        _graph_keys.pop(next(iter(_graph_keys)))
+    key = _next_graph_key[0]
+    _next_graph_key[0] += 1
+    _graph_keys[k] = (key, ii, jj)
+    return key
+
+
+def ba(*args, _ctx=None):
     """droid_backends.ba -- dense bundle adjustment, in place on poses[t0:t1] and disps[unique(ii)].
 
     ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm,
@@ -121,6 +143,8 @@ def ba(*args):
     ba(poses, disps, intrinsics, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
        motion_only)                                       (14 args, depth_video.pyc cuda_ba@232)
     Returns [dx, dz] of the last iteration (dx [t1-t0,6]; dz [M,ht,wd], empty when motion_only).
+    Asynchronous on the current stream when the same `ii` / `jj` tensor objects were seen by the previous call
+    (see _graph_key); a new edge list costs one stream synchronisation (the plan is built on the host).
     """
     if len(args) == 14:
         args = args[:3] + (None,) + args[3:]
@@ -131,16 +155,18 @@ def ba(*args):
     motion_only = bool(motion_only)
     N, ht, wd, E, M = _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, motion_only, True)
     t0, t1, iterations = int(t0), int(t1), int(iterations)
-    ctx = context(poses.device)
-    dx = torch.zeros((max(t1 - t0, 0), 6), dtype=torch.float32, device=poses.device)
-    dz = torch.zeros((0 if motion_only else M, ht, wd), dtype=torch.float32, device=poses.device)
+    ctx = _ctx if _ctx is not None else context(poses.device)
+    alloc = torch.empty if (iterations > 0 and E > 0) else torch.zeros          # both are fully written by the call
+    dx = alloc((max(t1 - t0, 0), 6), dtype=torch.float32, device=poses.device)
+    dz = alloc((0 if motion_only else M, ht, wd), dtype=torch.float32, device=poses.device)
     sens = disps_sens if (disps_sens is not None and disps_sens.numel() > 0) else None
+    key = _graph_key(ii, jj) if E > 0 else 0
     with torch.cuda.device(poses.device):
         stream = torch.cuda.current_stream(poses.device).cuda_stream
-        rc = ctx.lib.dba_ba(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(sens), _ptr(targets),
-                            _ptr(weights), _ptr(eta if not motion_only else None), _ptr(ii), _ptr(jj), E, N, ht, wd,
-                            M, t0, t1, iterations, float(lm), float(ep), int(motion_only), _ptr(dx), _ptr(dz),
-                            C.c_void_p(stream))
+        rc = ctx.lib.dba_ba_cached(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(sens), _ptr(targets),
+                                   _ptr(weights), _ptr(eta if not motion_only else None), _ptr(ii), _ptr(jj), E, N, ht,
+                                   wd, M, t0, t1, iterations, float(lm), float(ep), int(motion_only), _ptr(dx), _ptr(dz),
+                                   C.c_void_p(stream), key, C.c_void_p(0), C.c_void_p(0))
     ctx.check(rc)
     return [dx, dz]
 
@@ -163,12 +189,12 @@ def depth_cov(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, j
 
 
 def ba_host(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep,
-            motion_only, device=None):
+            motion_only, device=None, _ctx=None):
     """Same op on HOST tensors (pinned for full copy speed): copies in, runs, copies poses/disps back.
     The end-to-end entry point bench.py times (dba_ba_host)."""
     motion_only = bool(motion_only)
     N, ht, wd, E, M = _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, motion_only, False)
-    ctx = context(device)
+    ctx = _ctx if _ctx is not None else context(device)
     dx = torch.zeros((max(int(t1) - int(t0), 0), 6), dtype=torch.float32)
     sens = disps_sens if (disps_sens is not None and disps_sens.numel() > 0) else None
     with torch.cuda.device(ctx.device_index):
@@ -366,17 +392,17 @@ def debug_system(device=None):
     return buf[:n6, :n6].clone(), buf[n6, :n6].clone(), list(dims)
 
 
-def last_launch_count(device=None):
-    ctx = context(device)
+def last_launch_count(device=None, _ctx=None):
+    ctx = _ctx if _ctx is not None else context(device)
     return int(ctx.lib.dba_last_launch_count(ctx.handle))
 
 
 STAGES = ("linearize", "assemble", "allreduce", "cholesky", "backsub", "retract")
 
 
-def stage_times(device=None):
+def stage_times(device=None, _ctx=None):
     """Per-stage device time accumulated while the "profile" option was on: ({stage: ms}, LM iterations)."""
-    ctx = context(device)
+    ctx = _ctx if _ctx is not None else context(device)
     buf = (C.c_double * 8)()
     n = ctx.lib.dba_debug_read(ctx.handle, b"stage_ms", buf, C.sizeof(buf))
     if n < 0:

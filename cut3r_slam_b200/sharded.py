@@ -48,7 +48,11 @@ class ShardedBA:
 
     def __init__(self, device):
         self.device = torch.device(device)
-        self.ctx = droid_backends.context(self.device)
+        # a PRIVATE libdba context: once the communicator is attached every `ba` through this context all-reduces
+        # its reduced system, so plain droid_backends.ba / depth_cov calls (the module-level per-device context:
+        # frontend windows, motion-only BA, a graph that differs per rank) must not share it
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.ctx = droid_backends._Ctx(idx)
         self.rank, self.nranks = 0, 1
 
     def init_comm(self):
@@ -75,7 +79,13 @@ class ShardedBA:
         a full replica (updated identically on every rank); disps rows of ITS source keyframes are
         updated, the others are stale until `gather_disps`."""
         return droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
-                                 iterations, lm, ep, False)
+                                 iterations, lm, ep, False, _ctx=self.ctx)
+
+    def last_launch_count(self):
+        return droid_backends.last_launch_count(_ctx=self.ctx)
+
+    def stage_times(self):
+        return droid_backends.stage_times(_ctx=self.ctx)
 
     def gather_disps(self, disps, shards):
         """Make every rank's disps complete again: each rank broadcasts the rows of its keyframes."""

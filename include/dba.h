@@ -50,12 +50,28 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value);
  *   eta     [M,ht,wd], M = |unique(ii)|, rows in sorted(unique(ii)) order (ignored if motion_only)
  *   ii, jj  [E] int64 device
  *   dx_out  [t1-t0,6] or NULL, dz_out [M,ht,wd] or NULL: update of the LAST iteration
- * Synchronises `stream` once at entry when the edge lists differ from the cached plan's (they are
- * copied to the host to build the plan); the iteration loop itself never touches the host. */
+ * Host synchronisation: the plan (edge CSR + gather lists) is built on the host, so dba_ba copies ii / jj to the
+ * host and synchronises `stream` ONCE AT ENTRY ON EVERY CALL (it then compares them with the cached plan's lists and
+ * rebuilds only when they differ).  The iteration loop itself never touches the host.  Callers that re-use one edge
+ * list for several calls (FactorGraph.update: depth_video.pyc cuda_ba@232 is called once per update with the same
+ * ii / jj until the graph changes) use dba_ba_cached below, which does not synchronise on a hit. */
 int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
            const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
            int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
            int motion_only, float* dx_out, float* dz_out, void* stream);
+
+/* dba_ba with a caller-supplied identity of the edge lists.  graph_key != 0 and equal to the key the cached plan
+ * was built under (same E, N, ht, wd, t0, t1, motion_only): the plan is re-used WITHOUT reading ii / jj -- no copy,
+ * no host synchronisation, the call is fully asynchronous on `stream`.  Otherwise the plan is rebuilt from
+ * ii_host / jj_host (HOST copies of the lists, may be NULL) or, when those are NULL, from the device lists after one
+ * synchronising copy, and remembered under graph_key.  The caller guarantees that equal keys mean equal lists
+ * (cut3r_slam_b200/droid_backends.py derives the key from the tensors' storage address + version counter and keeps
+ * the tensors alive while the key is cached).  graph_key = 0 behaves like dba_ba. */
+int dba_ba_cached(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                  const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
+                  int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
+                  int motion_only, float* dx_out, float* dz_out, void* stream, uint64_t graph_key,
+                  const int64_t* ii_host, const int64_t* jj_host);
 
 /* Same, but every buffer is HOST memory (pinned for full speed): inputs are copied to the device,
  * the iterations run, poses/disps (and dx_out/dz_out if non-NULL) are copied back; returns after

@@ -26,7 +26,10 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     names = sys.argv[1:] or ["frontend", "backend"]
-    # single-GPU results of the whole graphs first (rank 0, no communicator yet)
+    sh = ShardedBA(dev)
+    sh.init_comm()
+    # single-GPU results of the whole graphs on rank 0, computed AFTER the communicator exists: ShardedBA owns a
+    # private libdba context, plain droid_backends.ba calls must neither all-reduce nor hang (sharded.py:51)
     single = {}
     if rank == 0:
         for name in names:
@@ -35,8 +38,6 @@ def main():
             torch.cuda.synchronize()
             single[name] = (s.poses.clone(), s.disps.cpu())
     dist.barrier()
-    sh = ShardedBA(dev)
-    sh.init_comm()
     ok = True
     for name in names:
         p = make_problem(name)
