@@ -102,6 +102,8 @@ struct dba_ctx {
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
   bool opt_tc = true;
+  bool opt_v2 = true;                // narrow keyframes on the one-warp-per-edge kernel (dba_linearize_v2.cu)
+  bool plan_v2 = false;              // ... and the cached plan was split for it
   int opt_wide_tc = 2;               // 0: SIMT above out-degree 20; 1: WIDE tcgen05 variant up to 25; 2: up to 41          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
@@ -183,6 +185,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
     if (n_tc_kf > 0 && linearize_tc_smem_bytes(degmax_tc) > ctx->smem_cap) n_tc_kf = 0;
   }
   const bool use_tc = n_tc_kf > 0;
+  const bool use_v2 = use_tc && ctx->opt_v2 && linearize_v2_smem_bytes(degmax_tc) <= ctx->smem_cap;
   int ppl = use_tc ? linearize_tc_ppl()
                    : (ctx->opt_ppl > 0 ? ctx->opt_ppl : linearize_pick_ppl(degmax, degmax + 1, motion_only, HW, ctx->smem_cap));
   if (ppl == 0 || linearize_smem_bytes(degmax, ppl, motion_only) > ctx->smem_cap)
@@ -204,7 +207,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
       }
       std::sort(degs.begin(), degs.end(), std::greater<int>());
       std::sort(wide.begin(), wide.end(), std::greater<int>());
-      const int slots = 2 * sm;
+      const int slots = use_v2 ? sm : 2 * sm;          // v2: one CTA per SM
       double best = 1e300;
       // measured (backend graph, 1 GPU): flat optimum for 2..5 waves of CTAs, clearly slower below; so only
       // split counts that give >= 3 waves compete (capped at 2 tiles per CTA), the simulation picks among them
@@ -218,6 +221,28 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
         std::priority_queue<double, std::vector<double>, std::greater<double>> free_at;
         for (int i = 0; i < slots; ++i) free_at.push(0.0);
         double makespan = 0.0;
+        // the SIMT CTAs of the wide keyframes start first (side stream) and take a whole SM = two slots;
+        // measured: a 64-pixel tile costs ~0.064 (deg+1)^2 of the unit in which a tcgen05 tile costs deg + 6
+        if (use_v2) {
+          // one CTA per SM for every kernel.  Unit ~ one v2 tile (one warp per edge: the tile time hardly depends on
+          // the out-degree); a WIDE tcgen05 tile of out-degree d costs ~0.25 (d + 1) of it
+          for (int dgk : wide)
+            for (int sp = 0; sp < S_c; ++sp) {
+              const int nt = std::min(tps_c, ntilesT - sp * tps_c);
+              const double t0s = free_at.top(); free_at.pop();
+              const double t1s = t0s + 1.0 + nt * 0.25 * (dgk + 1.0);
+              free_at.push(t1s);
+              if (t1s > makespan) makespan = t1s;
+            }
+          for (int dgk : degs)
+            for (int sp = 0; sp < S_c; ++sp) {
+              const int nt = std::min(tps_c, ntilesT - sp * tps_c);
+              const double t0s = free_at.top(); free_at.pop();
+              const double t1s = t0s + 1.0 + nt * (1.0 + 0.03 * dgk);
+              free_at.push(t1s);
+              if (t1s > makespan) makespan = t1s;
+            }
+        } else {
         // the SIMT CTAs of the wide keyframes start first (side stream) and take a whole SM = two slots;
         // measured: a 64-pixel tile costs ~0.064 (deg+1)^2 of the unit in which a tcgen05 tile costs deg + 6
         for (int dgk : wide)
@@ -238,6 +263,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
             free_at.push(t1s);
             if (t1s > makespan) makespan = t1s;
           }
+        }
         const double score = makespan * (1.0 + 0.01 * S_c);         // partial slabs cost assembly traffic
         if (score < best) { best = score; S = S_c; }
       }
@@ -250,6 +276,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   const int tps = (ntilesT + S - 1) / S;
   S = (ntilesT + tps - 1) / tps;     // no empty split
   if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
+  ctx->plan_v2 = use_v2;
   ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW; ctx->plan_ht = ht; ctx->plan_wd = wd;
 
   // kernel assignment of the source keyframes
@@ -405,7 +432,9 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
         CK(cudaEventRecord(ctx->ev_join, ctx->side), "join");
         if (sw != s2) CK(cudaEventRecord(ctx->ev_join2, sw), "join");
       }
-      if (g.n_tc > 0)
+      if (g.n_tc > 0 && ctx->plan_v2)
+        CK(launch_linearize_v2(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, st), "linearize (v2)");
+      else if (g.n_tc > 0)
         CK(launch_linearize_tc(g, in, ws, ctx->plan_tps, g.tc_list, g.n_tc, g.degmax_tc, 0, st), "linearize (tcgen05)");
       if (fork) {
         CK(cudaStreamWaitEvent(st, ctx->ev_join, 0), "join");
@@ -547,6 +576,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
   else if (n == "tensor_cores") { ctx->opt_tc = value != 0; ctx->plan_valid = false; }
+  else if (n == "linearize_v2") { ctx->opt_v2 = value != 0; ctx->plan_valid = false; }
   else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = int(value); ctx->plan_valid = false; }
   else if (n == "small_system") ctx->opt_small = value != 0;
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);

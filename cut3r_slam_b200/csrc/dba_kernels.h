@@ -62,6 +62,11 @@ cudaError_t launch_linearize(const DeviceGraph& g, const BAInputs& in, const Wor
 cudaError_t launch_linearize_tc(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
                                 const int32_t* kf_list, int nkf, int degmax, int wide, cudaStream_t st);
 size_t linearize_tc_smem_bytes(int degmax, int wide = 0);
+// second generation (dba_linearize_v2.cu): one warp per edge, out-degree <= linearize_v2_max_degree()
+cudaError_t launch_linearize_v2(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, int tiles_per_split,
+                                const int32_t* kf_list, int nkf, int degmax, cudaStream_t st);
+size_t linearize_v2_smem_bytes(int degmax);
+int linearize_v2_max_degree();
 int linearize_tc_wide_max_degree(int level);
 extern int g_tc_stream_mode;
 int linearize_tc_max_degree();
