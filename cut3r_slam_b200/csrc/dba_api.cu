@@ -225,12 +225,13 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
         // measured: a 64-pixel tile costs ~0.064 (deg+1)^2 of the unit in which a tcgen05 tile costs deg + 6
         if (use_v2) {
           // one CTA per SM for every kernel.  Unit ~ one v2 tile (one warp per edge: the tile time hardly depends on
-          // the out-degree); a WIDE tcgen05 tile of out-degree d costs ~0.25 (d + 1) of it
+          // the out-degree); a WIDE tcgen05 tile of out-degree d costs ~0.1 (d + 1) of it; a CTA costs ~1.4 tiles of
+          // prologue + epilogue (split sweep, profiles/r2_linearize_v2.md)
           for (int dgk : wide)
             for (int sp = 0; sp < S_c; ++sp) {
               const int nt = std::min(tps_c, ntilesT - sp * tps_c);
               const double t0s = free_at.top(); free_at.pop();
-              const double t1s = t0s + 1.0 + nt * 0.25 * (dgk + 1.0);
+              const double t1s = t0s + 1.4 + nt * 0.1 * (dgk + 1.0);
               free_at.push(t1s);
               if (t1s > makespan) makespan = t1s;
             }
@@ -238,7 +239,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
             for (int sp = 0; sp < S_c; ++sp) {
               const int nt = std::min(tps_c, ntilesT - sp * tps_c);
               const double t0s = free_at.top(); free_at.pop();
-              const double t1s = t0s + 1.0 + nt * (1.0 + 0.03 * dgk);
+              const double t1s = t0s + 1.4 + nt * (1.0 + 0.03 * dgk);      // measured: ~6 us per CTA, ~4.3 us per tile
               free_at.push(t1s);
               if (t1s > makespan) makespan = t1s;
             }

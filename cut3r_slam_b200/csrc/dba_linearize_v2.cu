@@ -33,7 +33,7 @@ constexpr int ACC_COLS = 128;          // TMEM columns per accumulator
 template <int NW>
 __host__ __device__ constexpr size_t v2_smem_bytes() {
   return size_t(2 * KB) * TILE_BYTES_128 +
-         sizeof(float) * (size_t(128) * ACS + NW * 12 + T + 6 * T + size_t(NW) * PS + (size_t(6) * (NW + 1) + 1) * T) +
+         sizeof(float) * (size_t(128) * ACS + NW * 12 + T + 5 * T + 6 * T + size_t(NW) * PS + (size_t(6) * (NW + 1) + 1) * T) +
          2 * sizeof(uint64_t) + 16;
 }
 
@@ -65,7 +65,8 @@ k_linearize_v2(const LinParams P) {
   float* sAcc = reinterpret_cast<float*>(smem_raw + 2 * KB * TILE);   // [128][ACS] running sums of the tile products
   float* sRt = sAcc + 128 * ACS;                            // [NW][12]
   float* ssq = sRt + NW * 12;                               // [T] sqrt(Q)
-  float* spx = ssq + T;                                     // [2][3][T]: x0, y0, d of the tile's pixels (double-buffered)
+  float* ssum = ssq + T;                                    // [5][T]: ck, wk, G summed over the keyframe's edges
+  float* spx = ssum + 5 * T;                                // [2][3][T]: x0, y0, d of the tile's pixels (double-buffered)
   float* spart = spx + 6 * T;                               // [NW][PS]: the edge's ck, wk, G per pixel
   float* spanel = spart + NW * PS;                          // [6 (deg+1) + 1][T]: rows 0-5 E_ii, 6 (1+e).. edge e, last w
   uint64_t* mbar = reinterpret_cast<uint64_t*>(spanel + (6 * (NW + 1) + 1) * T);   // [2]
@@ -88,15 +89,27 @@ k_linearize_v2(const LinParams P) {
   const float* dk = P.disps + int64_t(k) * HW;
   const bool owner = warp < deg;                            // this warp owns edge `warp` of the keyframe
 
+  const float inv_wd = 1.0f / float(P.wd);
   auto fill_px = [&](int tile, int pl, float dval) {        // pinhole.py:6-25
     float* b = spx + (tile & 1) * 3 * T;
     const int p = tile * T + pl;
-    const int py = p / P.wd, px = p - py * P.wd;
+    const int py = __float2int_rd((float(p) + 0.5f) * inv_wd), px = p - py * P.wd;   // exact for p < 2^22
     b[pl] = (float(px) - cx) / fx;
     b[T + pl] = (float(py) - cy) / fy;
     b[2 * T + pl] = dval;
   };
 
+  // ---- the edge's streamed inputs, one tile ahead; the 27 sums of Hjj / vj in registers for the whole CTA ------
+  const float* tg = P.targets;
+  const float* wg = P.weights;
+  float cur[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) cur[i] = 0.f;
+  if (owner) {
+    const int64_t eo = int64_t(P.cedge[e0 + warp]) * 2 * HW;
+    tg += eo; wg += eo;
+    if (tile_lo < tile_hi) load_inputs<STREAM>(tg, wg, HW, tile_lo * T, lane, cur);
+  }
   if (owner && lane == 0) relative_pose_Rt(P.poses, k, P.cj[e0 + warp], sRt + 12 * warp);
   if (tid < T && tile_lo < tile_hi) fill_px(tile_lo, tid, (tile_lo * T + tid < HW) ? __ldg(dk + tile_lo * T + tid) : 0.f);
   if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
@@ -112,49 +125,44 @@ k_linearize_v2(const LinParams P) {
   tc_fence_after_sync();
   const uint32_t tmem = *tmem_p;
 
-  // ---- the edge's streamed inputs, one tile ahead; the 27 sums of Hjj / vj in registers for the whole CTA ------
-  const float* tg = P.targets;
-  const float* wg = P.weights;
-  float cur[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) cur[i] = 0.f;
-  if (owner) {
-    const int64_t eo = int64_t(P.cedge[e0 + warp]) * 2 * HW;
-    tg += eo; wg += eo;
-    if (tile_lo < tile_hi) load_inputs<STREAM>(tg, wg, HW, tile_lo * T, lane, cur);
-  }
   float hs[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) hs[i] = 0.f;
 
-  // phase 2 mapping: 8 threads per pixel (threads 0..511); part 0 carries eta, part 1 the next tile's disparity
-  const int pl2 = tid >> 3, part = tid & 7;
+  // phase 2 mapping: warps 0-1, one thread per pixel of the tile (the other warps flush the previous tile meanwhile)
+  const int pl2 = tid;
   const float* etak = P.eta + int64_t(m) * HW;
   float eta_c = 0.f;
-  if (tid < 8 * T && part == 0 && tile_lo < tile_hi && tile_lo * T + pl2 < HW) eta_c = __ldg(etak + tile_lo * T + pl2);
+  if (tid < T && tile_lo < tile_hi && tile_lo * T + pl2 < HW) eta_c = __ldg(etak + tile_lo * T + pl2);
 
-  // flush mapping: quarter q = warp & 3 (TMEM lanes 32 q ..), the quarter's column groups round-robin over its warps
-  const int fq = warp & 3, fj = warp >> 2;
+  // flush mapping: warps 2.. ; quarter q = warp & 3 (TMEM lanes 32 q ..), the quarter's 16-column groups round-robin
+  // over its flush warps (quarters 0 and 1 lend warps 0 and 1 to phase 2)
+  const int fq = warp & 3;
+  const int fj = (warp >> 2) - (fq < 2 ? 1 : 0);
+  const int fnq = NW / 4 - (fq < 2 ? 1 : 0);
   const int frow = 32 * fq + lane;
   const uint32_t tlane = uint32_t(32 * fq) << 16;
   const int fmaxg = (6 * ((32 * fq + 31) / 6) + 5) >> 4;    // last 16-column group any row of this quarter needs
   const int gw = R >> 4;                                    // group of the w column
   const int ngroups = N >> 4;
   auto flush = [&](int buf) {
-    if (32 * fq >= R) return;                               // warp-uniform: no panel rows in this quarter
-    for (int g = fj; g < ngroups; g += NW / 4) {
+    if (warp < 2 || 32 * fq >= R) return;                   // warp-uniform
+    for (int g = fj; g < ngroups; g += fnq) {
       if (g > fmaxg && g != gw) continue;                   // warp-uniform
       uint32_t v[16];
       tmem_ld16(tmem + tlane + uint32_t(buf * ACC_COLS + 16 * g), v);
-      tmem_ld_wait();
       float4* a = reinterpret_cast<float4*>(sAcc + frow * ACS + 16 * g);
+      float4 t4[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) t4[c] = a[c];
+      tmem_ld_wait();
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        float4 t4 = a[c];
-        t4.x += __uint_as_float(v[4 * c + 0]); t4.y += __uint_as_float(v[4 * c + 1]);
-        t4.z += __uint_as_float(v[4 * c + 2]); t4.w += __uint_as_float(v[4 * c + 3]);
-        a[c] = t4;
+        t4[c].x += __uint_as_float(v[4 * c + 0]); t4[c].y += __uint_as_float(v[4 * c + 1]);
+        t4[c].z += __uint_as_float(v[4 * c + 2]); t4[c].w += __uint_as_float(v[4 * c + 3]);
       }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) a[c] = t4[c];
     }
   };
 
@@ -162,17 +170,13 @@ k_linearize_v2(const LinParams P) {
   for (int tile = tile_lo; tile < tile_hi; ++tile) {
     const int p0 = tile * T;
     const float* px = spx + (tile & 1) * 3 * T;
-    float pre_n = 0.f;                                      // part 0: eta, part 1: d of pixel (tile+1, pl2)
-    if (tid < 8 * T && tile + 1 < tile_hi && part < 2) {
+    float eta_n = 0.f, d_n = 0.f;                           // warps 0-1: eta and disparity of pixel (tile + 1, pl2)
+    if (warp < 2 && tile + 1 < tile_hi) {
       const int pn = p0 + T + pl2;
-      if (pn < HW) pre_n = __ldg((part == 0 ? etak : dk) + pn);
+      if (pn < HW) { eta_n = __ldg(etak + pn); d_n = __ldg(dk + pn); }
     }
     // ---------------- phase 1: the warp's edge, lanes own pixels lane and lane + 32 ---------------------------
     if (owner) {
-      float nxt[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) nxt[i] = 0.f;
-      if (tile + 1 < tile_hi) load_inputs<STREAM>(tg, wg, HW, p0 + T, lane, nxt);
       float Rt[12];
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
@@ -225,62 +229,83 @@ k_linearize_v2(const LinParams P) {
         sp[3 * T + pl] = Rt[1] * hx + Rt[4] * hy + Rt[7] * hz;
         sp[4 * T + pl] = Rt[2] * hx + Rt[5] * hy + Rt[8] * hz;
       }
+      // the next tile's inputs are requested AFTER this tile's were consumed: the scoreboards are counters, a wait
+      // for `cur` issued after newer loads would wait for those too (ncu r2h: 7 % of the samples stalled there)
+      asm volatile("" ::: "memory");
 #pragma unroll
-      for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
+      for (int i = 0; i < 8; ++i) cur[i] = 0.f;
+      if (tile + 1 < tile_hi) load_inputs<STREAM>(tg, wg, HW, p0 + T, lane, cur);
     }
     __syncthreads();
-    // ---------------- phase 2: eight threads per pixel sum the edges' partials in a fixed order ----------------
-    if (tid < 8 * T) {
+    // ---------------- phase 2 (warps 0-1, one pixel each): the edges' partials summed in a fixed order; the other
+    // warps meanwhile add the PREVIOUS tile's tensor-core products into the shared-memory accumulator ------------
+    if (tile > tile_lo) {   // MMAs of the previous tile done: its accumulator readable, operand tiles reusable
+      mbar_wait(&mbar[(tile - tile_lo - 1) & 1], uint32_t((tile - tile_lo - 1) >> 1) & 1u);
+      tc_fence_after_sync();
+    }
+    if (warp < 8) {         // four threads per pixel sum the edges' partials (fixed order), lane 0 of the four stores
+      const int plr = tid >> 2, part = tid & 3;
       float sum[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int w = part; w < deg; w += 8) {
-        const float* spw = spart + w * PS + pl2;
+      for (int w = part; w < deg; w += 4) {
+        const float* spw = spart + w * PS + plr;
 #pragma unroll
         for (int i = 0; i < 5; ++i) sum[i] += spw[i * T];
       }
 #pragma unroll
-      for (int mk = 1; mk <= 4; mk <<= 1)
+      for (int mk = 1; mk <= 2; mk <<= 1)
 #pragma unroll
         for (int i = 0; i < 5; ++i) sum[i] += __shfl_xor_sync(0xffffffffu, sum[i], mk);
-      if (part == 1 && tile + 1 < tile_hi) fill_px(tile + 1, pl2, pre_n);
       if (part == 0) {
-        const int p = p0 + pl2;
-        const bool inb = p < HW;
-        const float dd = px[2 * T + pl2], xx = px[pl2], yy = px[T + pl2];
-        float C = sum[0], wsum = sum[1];
-        const float Gx = sum[2], Gy = sum[3], Gz = sum[4];
-        float Qv = 0.f, wv = 0.f;
-        if (inb) {
-          const float et = eta_c;
-          if (P.disps_sens != nullptr) {
-            const float ds = __ldg(P.disps_sens + int64_t(k) * HW + p);
-            const float ms = ds > 0.f ? 1.f : 0.f;
-            C = C + ms * kSensAlpha + (1.f - ms) * et + kCEps;
-            wsum = wsum - ms * kSensAlpha * (dd - ds);
-          } else {
-            C = C + et + kCEps;                             // ba.py:92
-          }
-          Qv = 1.0f / C;
-          wv = wsum;
-          P.Q[int64_t(m) * HW + p] = Qv;
-          P.w[int64_t(m) * HW + p] = wv;
-        }
-        ssq[pl2] = sqrtf(Qv);
-        spanel[R * T + pl2] = wv;                           // operand row R
-        spanel[0 * T + pl2] = -dd * Gx;                     // E_ii = -[d G, X0 x G],  X0 = [xx, yy, 1]
-        spanel[1 * T + pl2] = -dd * Gy;
-        spanel[2 * T + pl2] = -dd * Gz;
-        spanel[3 * T + pl2] = -(yy * Gz - Gy);
-        spanel[4 * T + pl2] = -(Gx - xx * Gz);
-        spanel[5 * T + pl2] = -(xx * Gy - yy * Gx);
-        eta_c = pre_n;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) ssum[i * T + plr] = sum[i];
       }
     }
     __syncthreads();
-    // ---------------- phase 3: operands for the tensor core ----------------------------------------------------
-    if (tile > tile_lo) {   // MMAs of the previous tile done: operand tiles reusable, its accumulator readable
-      mbar_wait(&mbar[(tile - tile_lo - 1) & 1], uint32_t((tile - tile_lo - 1) >> 1) & 1u);
-      tc_fence_after_sync();
+    if (warp < 2) {         // one thread per pixel: Q, w, the source-pose rows
+      float sum[5];
+#pragma unroll
+      for (int i = 0; i < 5; ++i) sum[i] = ssum[i * T + pl2];
+      const int p = p0 + pl2;
+      const bool inb = p < HW;
+      const float dd = px[2 * T + pl2], xx = px[pl2], yy = px[T + pl2];
+      float C = sum[0], wsum = sum[1];
+      const float Gx = sum[2], Gy = sum[3], Gz = sum[4];
+      float Qv = 0.f, wv = 0.f, sq = 0.f;
+      if (inb) {
+        const float et = eta_c;
+        if (P.disps_sens != nullptr) {
+          const float ds = __ldg(P.disps_sens + int64_t(k) * HW + p);
+          const float ms = ds > 0.f ? 1.f : 0.f;
+          C = C + ms * kSensAlpha + (1.f - ms) * et + kCEps;
+          wsum = wsum - ms * kSensAlpha * (dd - ds);
+        } else {
+          C = C + et + kCEps;                               // ba.py:92
+        }
+        float rs;                                           // sqrt(Q) = C^-1/2: MUFU.RSQ + one Newton step (~0.5 ulp)
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(C));
+        rs = rs * fmaf(-0.5f * C, rs * rs, 1.5f);
+        sq = rs;
+        Qv = rs * rs;
+        wv = wsum;
+        P.Q[int64_t(m) * HW + p] = Qv;
+        P.w[int64_t(m) * HW + p] = wv;
+      }
+      ssq[pl2] = sq;
+      spanel[R * T + pl2] = wv;                             // operand row R
+      spanel[0 * T + pl2] = -dd * Gx;                       // E_ii = -[d G, X0 x G],  X0 = [xx, yy, 1]
+      spanel[1 * T + pl2] = -dd * Gy;
+      spanel[2 * T + pl2] = -dd * Gz;
+      spanel[3 * T + pl2] = -(yy * Gz - Gy);
+      spanel[4 * T + pl2] = -(Gx - xx * Gz);
+      spanel[5 * T + pl2] = -(xx * Gy - yy * Gx);
+      eta_c = eta_n;
+      if (tile + 1 < tile_hi) fill_px(tile + 1, pl2, d_n);
+    } else if (tile > tile_lo) {
+      flush(((tile - tile_lo) & 1) ^ 1);
+      tc_fence_before_sync();
     }
+    __syncthreads();
+    // ---------------- phase 3: operands for the tensor core ----------------------------------------------------
     {
       // half a warp per operand row, lane = 4 consecutive pixels = one 16-byte chunk of the swizzled K-major tile:
       // v * sqrt(Q) -> hi = tf32(v), lo = v - hi.  Rows advance by 2 NW (a multiple of 8): constant byte stride.
@@ -307,7 +332,7 @@ k_linearize_v2(const LinParams P) {
     fence_proxy_async_smem();
     __syncthreads();
     const int buf = (tile - tile_lo) & 1;
-    if (tid == 0) {
+    if (tid == NT - 32) {                                   // the last warp owns an edge only when deg == NW
       tc_fence_after_sync();
       const uint32_t idesc = make_idesc_tf32(128, N);
       const uint32_t ah = smem_u32(hi), al = smem_u32(lo);
@@ -330,11 +355,6 @@ k_linearize_v2(const LinParams P) {
           mma_tf32_ss(acc, dh, dh, idesc, true);
         }
       mma_commit(&mbar[buf]);
-    }
-    // ---------------- flush of the PREVIOUS tile's products while this tile's MMAs run --------------------------
-    if (tile > tile_lo) {
-      flush(buf ^ 1);
-      tc_fence_before_sync();
     }
   }
   if (tile_lo < tile_hi) {
