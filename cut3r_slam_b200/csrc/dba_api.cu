@@ -105,6 +105,7 @@ struct dba_ctx {
   bool opt_v2 = true;                // narrow keyframes on the one-warp-per-edge kernel (dba_linearize_v2.cu)
   bool plan_v2 = false;              // ... and the cached plan was split for it
   int opt_wide_tc = 2;               // 0: SIMT above out-degree 20; 1: WIDE tcgen05 variant up to 25; 2: up to 41          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
+  int opt_refine = 1;                // iterative refinement of the pose solve: 0 off, 1 auto, 2 every iteration
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
   int64_t* h_idx = nullptr;
@@ -372,7 +373,7 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
   if (ctx->coop_n != P.n6) { ctx->coop_ctas = cholesky_coop_max_ctas(P.n6); ctx->coop_n = P.n6; }
   CK(ctx->dx.ensure(size_t(P.n6) * f + 16), "workspace");
   CK(ctx->fail.ensure(16, true), "workspace");
-  if (ctx->keep_system) CK(ctx->Akeep.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
+  if (ctx->keep_system || ctx->opt_refine) CK(ctx->Akeep.ensure(size_t(P.n6 + 1) * ld * f), "workspace");
   ws.Hpart = ctx->Hpart.as<float>(); ws.Spart = ctx->Spart.as<float>(); ws.vEpart = ctx->vEpart.as<float>();
   ws.Q = ctx->Q.as<float>(); ws.w = ctx->w.as<float>(); ws.Hblk = ctx->Hblk.as<float>(); ws.vblk = ctx->vblk.as<float>();
   ws.A = ctx->A.as<float>(); ws.Lm = ctx->Lm.as<float>(); ws.ldA = ld; ws.Ldiag = ctx->Ldiag.as<float>(); ws.dx = ctx->dx.as<float>();
@@ -460,7 +461,14 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
         return 1000 + r;
       }
     }
-    if (ctx->keep_system)
+    // iterative refinement (dba_refine.cu) of the cooperative solve on the LAST iteration of the call: an earlier
+    // iteration's solver error (4e-4 of dx at n = 756, 6e-3 at n = 3060) is corrected by the next relinearisation,
+    // the last one's would stay in the result.  "refine" = 2: every iteration (costs two more triangular solves:
+    // +65 us at n = 756, +1 ms at n = 3060 with the single-CTA solves)
+    const bool coop_path = cov_out == nullptr && !(ctx->opt_small && g.n6 <= cholesky_small_max_n()) &&
+                           ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol;
+    const bool refine = coop_path && ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it == iterations - 1);
+    if (ctx->keep_system || refine)
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");
     mark();
@@ -475,8 +483,10 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     }
     if (ctx->opt_small && g.n6 <= cholesky_small_max_n())
       CK(launch_cholesky_small(ws, g.n6, st), "cholesky (single CTA)");
-    else if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol)
-      CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st), "cholesky (cooperative)");
+    else if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol) {
+      CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st, !refine), "cholesky (cooperative)");
+      if (refine) CK(launch_refine(ws, ctx->Akeep.as<float>(), g.n6, st), "refinement");
+    }
     else
       CK(launch_cholesky_solve(ws, g.n6, st), "cholesky");
     mark();
@@ -580,6 +590,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "linearize_v2") { ctx->opt_v2 = value != 0; ctx->plan_valid = false; }
   else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = int(value); ctx->plan_valid = false; }
   else if (n == "small_system") ctx->opt_small = value != 0;
+  else if (n == "refine") ctx->opt_refine = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {

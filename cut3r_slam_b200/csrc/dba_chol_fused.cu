@@ -381,7 +381,7 @@ constexpr int BCPT = 2;                  // columns per thread held in registers
 
 __global__ void __launch_bounds__(BSN)
 k_backsolve(const float* __restrict__ Lm, const float* __restrict__ Ldiag, int ld, int n, int* fail,
-            unsigned* bar, float* __restrict__ dx) {
+            unsigned* bar, float* __restrict__ dx, int mode) {
   extern __shared__ __align__(16) float bsm[];
   float* sLi = bsm;                      // [2][32][32] L_kk^-1 of the current / next block
   float* xs = bsm + 2 * NB * NB;         // [n + 32] running right-hand side -> solution
@@ -435,8 +435,9 @@ k_backsolve(const float* __restrict__ Lm, const float* __restrict__ Ldiag, int l
   __syncthreads();
   const int failed = *reinterpret_cast<volatile int*>(fail);
   __syncthreads();
-  for (int i = tid; i < n; i += BSN) dx[i] = failed ? 0.f : xs[i];
-  if (tid == 0) { *fail = 0; *bar = 0u; }
+  // mode bit 1: dx += x (the correction of an iterative-refinement pass); bit 0: last solve of the iteration
+  for (int i = tid; i < n; i += BSN) dx[i] = failed ? 0.f : ((mode & 2) ? dx[i] + xs[i] : xs[i]);
+  if (tid == 0 && (mode & 1)) { *fail = 0; *bar = 0u; }
 }
 
 
@@ -451,7 +452,7 @@ __host__ __device__ inline size_t backsolve_smem_floats(int n, int W) {
 
 __global__ void __launch_bounds__(BSN)
 k_backsolve_smem(const float* __restrict__ Lm, const float* __restrict__ Ldiag, int ld, int n, int W, int* fail,
-                 unsigned* bar, float* __restrict__ dx) {
+                 unsigned* bar, float* __restrict__ dx, int mode) {
   extern __shared__ __align__(16) float bsm[];
   float* sLi = bsm;                      // [2][32][32]
   float* slab = bsm + 2 * NB * NB;       // [2][32][W]
@@ -514,8 +515,9 @@ k_backsolve_smem(const float* __restrict__ Lm, const float* __restrict__ Ldiag, 
   __syncthreads();
   const int failed = *reinterpret_cast<volatile int*>(fail);
   __syncthreads();
-  for (int i = tid; i < n; i += BSN) dx[i] = failed ? 0.f : xs[i];
-  if (tid == 0) { *fail = 0; *bar = 0u; }
+  // mode bit 1: dx += x (the correction of an iterative-refinement pass); bit 0: last solve of the iteration
+  for (int i = tid; i < n; i += BSN) dx[i] = failed ? 0.f : ((mode & 2) ? dx[i] + xs[i] : xs[i]);
+  if (tid == 0 && (mode & 1)) { *fail = 0; *bar = 0u; }
 }
 
 
@@ -628,7 +630,7 @@ k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx
 void chol_trace_read(unsigned long long* out, int n) { cudaMemcpyFromSymbol(out, g_trace, sizeof(unsigned long long) * n); }
 #endif
 
-cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaStream_t st) {
+cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaStream_t st, bool finalize) {
   const int r0 = (n < NB) ? n : NB;
   const int ntj = (n - r0 + TT - 1) / TT, nti = (n + 1 - r0 + TT - 1) / TT;
   const int ntiles = ntj * (ntj + 1) / 2 + (nti > ntj ? ntj : 0);
@@ -641,16 +643,25 @@ cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaS
   cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_chol_fused), dim3(grid), dim3(NTH), args, 0, st);
   g_launch_count++;
   if (err != cudaSuccess) return err;
+  return launch_backsolve(ws, n, finalize ? 1 : 0, st);
+}
+
+// L^T x = y with y = row n of Lm; mode: bit 0 = last solve of the iteration (resets the flags), bit 1 = dx += x
+cudaError_t launch_backsolve(const Workspace& ws, int n, int mode, cudaStream_t st) {
+  const float* Lm = ws.Lm; const float* Ldiag = ws.Ldiag; int ld = ws.ldA; int* fail = ws.fail;
+  unsigned* bar = reinterpret_cast<unsigned*>(ws.fail + 1);
+  float* dx = ws.dx;
   const int nkb = (n + NB - 1) / NB;
   const int W = (nkb - 1) * NB > 0 ? (nkb - 1) * NB : 4;
+  cudaError_t err;
   if (W <= BSW_MAX) {
     const size_t smem = backsolve_smem_floats(n, W) * sizeof(float);
     err = cudaFuncSetAttribute(k_backsolve_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (err != cudaSuccess) return err;
-    k_backsolve_smem<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, W, fail, bar, dx);
+    k_backsolve_smem<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, W, fail, bar, dx, mode);
   } else {
     const size_t smem = size_t(2 * NB * NB + n + NB) * sizeof(float);
-    k_backsolve<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, fail, bar, dx);
+    k_backsolve<<<1, BSN, smem, st>>>(Lm, Ldiag, ld, n, fail, bar, dx, mode);
   }
   g_launch_count++;
   return cudaGetLastError();

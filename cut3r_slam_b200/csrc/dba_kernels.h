@@ -81,7 +81,11 @@ cudaError_t launch_cholesky_small(const Workspace& ws, int n6, cudaStream_t st);
 int cholesky_small_max_n();
 cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
 // single cooperative launch (one grid barrier per block step); max_ctas from cholesky_coop_max_ctas (0 = unavailable)
-cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st);
+cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st, bool finalize = true);
+cudaError_t launch_backsolve(const Workspace& ws, int n6, int mode, cudaStream_t st);
+// one step of iterative refinement after launch_cholesky_coop(..., finalize = false): r = rhs - S dx accumulated in fp64
+// from the saved system Sorig [(n6+1), ldA] (lower + rhs row), L y = r, L^T d = y, dx += d  (dba_refine.cu)
+cudaError_t launch_refine(const Workspace& ws, const float* Sorig, int n6, cudaStream_t st);
 int cholesky_coop_max_ctas(int n6);
 size_t cholesky_ldiag_floats(int n6);   // floats in Workspace::Ldiag
 cudaError_t launch_backsub(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, cudaStream_t st);

@@ -164,3 +164,20 @@ def test_full_size_host_entry_and_gauge(name):
     hp = [t.pin_memory() if isinstance(t, torch.Tensor) else t for t in h.ba_args()]
     db.ba_host(*hp)
     assert torch.equal(hp[0], poses) and torch.equal(hp[1], disps)
+
+
+def test_backend_eight_iteration_call_final_state():
+    """The bench's step: ONE call with 8 LM iterations on the backend graph (the pose solve is refined on the last
+    iteration only for systems this size, csrc/dba_api.cu): the final state against 8 oracle iterations."""
+    db = _db()
+    p = make_problem("backend")
+    a = list(p.ba_args())
+    p64, d64 = od.oracle_ba(*a, dtype=torch.float64)
+    p32, d32 = od.oracle_ba(*a, dtype=torch.float32)
+    g = p.to("cuda")
+    db.ba(*g.ba_args())
+    gap_d = rel_err(d32, d64)
+    assert rel_err(g.disps.cpu(), d64) < max(1e-4, MULT * gap_d), gap_d
+    gap_p = float(ose3.tangent_update(p32.double(), p64.double()).abs().max())
+    upd = float(ose3.tangent_update(g.poses.cpu().double(), p64.double()).abs().max())
+    assert upd < max(1e-4, MULT * gap_p), (upd, gap_p)
