@@ -31,6 +31,8 @@ SIGNATURES = {
                               C.c_void_p]),
     "dba_frame_distance": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int,
                                      C.c_float, c_f, C.c_void_p]),
+    "dba_covis_distance": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int, c_f,
+                                     C.c_void_p]),
     "dba_iproj": (C.c_int, [C.c_void_p, c_f, c_f, c_f, C.c_int64, C.c_int, C.c_int, c_f, C.c_void_p]),
     "dba_depth_filter": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_i, c_f, C.c_int64, C.c_int64, C.c_int, C.c_int, c_f,
                                    C.c_void_p]),

@@ -721,6 +721,20 @@ int dba_frame_distance(dba_ctx* ctx, const float* poses, const float* disps, con
   return 0;
 }
 
+int dba_covis_distance(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                       const int64_t* ii, int64_t K, int64_t N, int ht, int wd, float* out, void* stream) {
+  if (!ctx) return -1;
+  if (K < 0 || N <= 1 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size (needs at least two frames)");
+  if (K == 0) return 0;
+  if (!poses || !disps || !intrinsics || !ii || !out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_covis_distance(poses, disps, intrinsics, ii, K, int(N), ht, wd, out, reinterpret_cast<cudaStream_t>(stream)),
+     "covis_distance");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
 int dba_iproj(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, int64_t K, int ht,
               int wd, float* out, void* stream) {
   if (!ctx) return -1;

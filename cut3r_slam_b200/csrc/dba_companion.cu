@@ -70,6 +70,57 @@ k_frame_distance(const float* __restrict__ poses, const float* __restrict__ disp
   }
 }
 
+// covis_distance(poses, disps, intrinsics, ii) -> [K]  (call shape depth_video.pyc distance_covis@217; PARITY UNPINNED).
+// Definition used: for keyframe i = ii[k] and its temporal successor j = i + 1 (i - 1 for the last frame of the
+// buffer): the mean induced-flow magnitude |proj(G_ij X_i) - x_i| in pixels over the COVISIBLE pixels of frame i --
+// those whose transformed depth exceeds MIN_DEPTH and whose projection falls inside the image of frame j;
+// sentinel 1000 when no pixel is covisible.  The caller rescales by 1 / median(disps[ii]) (@218).
+__global__ void __launch_bounds__(256)
+k_covis_distance(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                 const int64_t* __restrict__ ii, int N, int HW, int wd, int ht, float* __restrict__ out) {
+  __shared__ float sRt[12];
+  __shared__ float sred[2][8];
+  const int64_t i = ii[blockIdx.x];
+  const int64_t j = (i + 1 < N) ? i + 1 : i - 1;
+  const bool ok = i >= 0 && i < N && j >= 0 && j < N;
+  if (threadIdx.x == 0 && ok) relative_pose_Rt(poses, int(i), int(j), sRt);
+  __syncthreads();
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  float num = 0.f, den = 0.f;
+  if (ok) {
+    float Rt[12];
+#pragma unroll
+    for (int t = 0; t < 12; ++t) Rt[t] = sRt[t];
+    for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+      const float d = disps[i * HW + p];
+      const int py = p / wd, px = p - py * wd;
+      const float xf = float(px), yf = float(py);
+      const float x0 = (xf - cx) / fx, y0 = (yf - cy) / fy;
+      const float X = Rt[0] * x0 + Rt[1] * y0 + Rt[2] + Rt[9] * d;
+      const float Y = Rt[3] * x0 + Rt[4] * y0 + Rt[5] + Rt[10] * d;
+      const float Z = Rt[6] * x0 + Rt[7] * y0 + Rt[8] + Rt[11] * d;
+      const float Zs = Z > kMinDepth ? Z : 1.f;
+      const float u = fx * (X / Zs) + cx, v = fy * (Y / Zs) + cy;
+      const bool vis = Z > kMinDepth && u >= 0.f && u <= float(wd - 1) && v >= 0.f && v <= float(ht - 1);
+      const float du = u - xf, dv = v - yf;
+      if (vis) { num += sqrtf(du * du + dv * dv); den += 1.f; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    num += __shfl_xor_sync(0xffffffffu, num, o);
+    den += __shfl_xor_sync(0xffffffffu, den, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { sred[0][warp] = num; sred[1][warp] = den; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float n = 0.f, dn = 0.f;
+    for (int w = 0; w < 8; ++w) { n += sred[0][w]; dn += sred[1][w]; }
+    out[blockIdx.x] = (!ok || dn < 1.0f) ? kFrameDistanceSentinel : n / dn;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 k_iproj(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr, int HW,
         int wd, float* __restrict__ out) {
@@ -147,6 +198,13 @@ cudaError_t launch_frame_distance(const float* poses, const float* disps, const 
                                   const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
                                   cudaStream_t st) {
   k_frame_distance<<<unsigned(K), 256, 0, st>>>(poses, disps, intr, ii, jj, N, ht * wd, wd, beta, out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_covis_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                  int64_t K, int N, int ht, int wd, float* out, cudaStream_t st) {
+  k_covis_distance<<<unsigned(K), 256, 0, st>>>(poses, disps, intr, ii, N, ht * wd, wd, ht, out);
   g_launch_count++;
   return cudaGetLastError();
 }

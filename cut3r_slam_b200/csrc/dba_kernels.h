@@ -97,6 +97,8 @@ cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Works
 cudaError_t launch_frame_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                                   const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
                                   cudaStream_t st);
+cudaError_t launch_covis_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                  int64_t K, int N, int ht, int wd, float* out, cudaStream_t st);
 cudaError_t launch_iproj(const float* poses, const float* disps, const float* intr, int64_t K, int ht, int wd,
                          float* out, cudaStream_t st);
 cudaError_t launch_depth_filter(const float* poses, const float* disps, const float* intr, const int64_t* ix,

@@ -227,6 +227,24 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta):
     return out
 
 
+def covis_distance(poses, disps, intrinsics, ii):
+    """droid_backends.covis_distance(poses, disps, intrinsics, ii) -> [K] fp32 (depth_video.pyc distance_covis@217).
+    Parity unpinned (reference CUDA absent); definition in include/dba.h and oracle/dba.py."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ii, "ii", torch.int64, 1)
+    N, ht, wd = disps.shape
+    K = ii.numel()
+    out = torch.empty((K,), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        ctx.check(ctx.lib.dba_covis_distance(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ii), K, N, ht,
+                                             wd, _ptr(out), C.c_void_p(stream)))
+    return out
+
+
 def iproj(poses, disps, intrinsics):
     """droid_backends.iproj(poses_inv, disps, intrinsics) -> [K,ht,wd,3] points G * (X0 / disp)."""
     _check(poses, "poses", torch.float32, 2)

@@ -86,6 +86,13 @@ int dba_frame_distance(dba_ctx* ctx, const float* poses, const float* disps, con
                        const int64_t* ii, const int64_t* jj, int64_t K, int64_t N, int ht, int wd, float beta,
                        float* out, void* stream);
 
+/* ---- covis_distance(poses, disps, intrinsics, ii) -> [K]  (depth_video.pyc distance_covis@217; HI-SLAM2 keyframe
+ * culling).  Reference CUDA absent -> PARITY UNPINNED; definition (oracle/dba.py covis_distance): mean induced-flow
+ * magnitude in pixels between keyframe ii[k] and its temporal successor over the pixels visible in both (transformed
+ * depth > 0.2 and projection inside the image), 1000 when none is.  The caller divides by median(disps[ii]). */
+int dba_covis_distance(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics,
+                       const int64_t* ii, int64_t K, int64_t N, int ht, int wd, float* out, void* stream);
+
 /* ---- iproj(poses_inv, disps, intrinsics) -> [K,ht,wd,3]  (hislam2/util/droid_visualization.py:97) */
 int dba_iproj(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, int64_t K, int ht,
               int wd, float* out, void* stream);

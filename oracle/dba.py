@@ -356,6 +356,32 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta=0.3):
     return torch.where(den < 1.0, torch.full_like(num, FRAME_DISTANCE_SENTINEL), num / den.clamp(min=1e-12))
 
 
+def covis_distance(poses, disps, intrinsics, ii):
+    """PARITY UNPINNED (call shape pyc:DepthVideo.distance_covis@217, which rescales the result by
+    1 / median(disps[ii]) @218).  Definition chosen: for keyframe i and its temporal successor j = i + 1 (i - 1 for
+    the last frame): mean induced-flow magnitude in pixels over the COVISIBLE pixels of frame i -- transformed depth
+    > MIN_DEPTH and projection inside the image of frame j; sentinel 1000 when no pixel is covisible."""
+    dt = poses.dtype
+    N, ht, wd = disps.shape
+    intr = intrinsics.to(dt)
+    fx, fy, cx, cy = intr.unbind(-1)
+    ii = ii.long()
+    jj = torch.where(ii + 1 < N, ii + 1, ii - 1)
+    X0, _ = iproj_pinhole(disps[ii], intr)
+    y, x = torch.meshgrid(torch.arange(ht, dtype=dt), torch.arange(wd, dtype=dt), indexing="ij")
+    Gij = se3.se3_mul(poses[jj], se3.se3_inv(poses[ii]))
+    X1 = se3.se3_act4(Gij[:, None, None, :], X0)
+    Z = X1[..., 2]
+    Zs = torch.where(Z > MIN_DEPTH, Z, torch.ones_like(Z))
+    u = fx * (X1[..., 0] / Zs) + cx
+    v = fy * (X1[..., 1] / Zs) + cy
+    vis = ((Z > MIN_DEPTH) & (u >= 0) & (u <= wd - 1) & (v >= 0) & (v <= ht - 1)).to(dt)
+    f = torch.sqrt((u - x) ** 2 + (v - y) ** 2) * vis
+    num = f.reshape(len(ii), -1).sum(-1)
+    den = vis.reshape(len(ii), -1).sum(-1)
+    return torch.where(den < 1.0, torch.full_like(num, FRAME_DISTANCE_SENTINEL), num / den.clamp(min=1.0))
+
+
 def iproj(poses, disps, intrinsics):
     """Back-projection to 3-D points (call shape hislam2/util/droid_visualization.py:97).
 

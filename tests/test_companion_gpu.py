@@ -130,3 +130,25 @@ def test_proximity_factors_from_device_distances(traj):
     b.add_factors([e[0] for e in es], [e[1] for e in es], remove=False)
     assert len(a) > 2 * (2 * t - 3)                               # something beyond the temporal edges was added
     assert a.ii.tolist() == b.ii and a.jj.tolist() == b.jj
+
+
+def test_covis_distance_matches_oracle(traj):
+    """covis_distance (depth_video.pyc distance_covis@217): reference CUDA absent -> pinned to the definition in
+    oracle/dba.py only (parity unpinned).  Pixels whose projection sits within 1e-3 px of the image border may be
+    classified differently in fp32 and fp64; the bound allows for a handful of them."""
+    db = _db()
+    p, g = traj, traj.to("cuda")
+    t = p.poses.shape[0]
+    ii = torch.arange(t)
+    d = db.covis_distance(g.poses, g.disps, g.intrinsics, ii.cuda()).cpu()
+    ref = od.covis_distance(p.poses.double(), p.disps.double(), p.intrinsics.double(), ii)
+    assert d.shape == (t,) and d.dtype == torch.float32
+    assert float(((d.double() - ref).abs() / ref.abs().clamp(min=1e-3)).max()) < 2e-3
+    assert db.covis_distance(g.poses, g.disps, g.intrinsics, ii[:0].cuda()).shape == (0,)
+    with pytest.raises(RuntimeError):
+        db.covis_distance(g.poses, g.disps, g.intrinsics, ii.int().cuda())
+    # looking away: nothing covisible -> sentinel
+    poses = g.poses[:2].clone()
+    poses[1, 3:] = torch.tensor([0.0, 1.0, 0.0, 0.0], device="cuda")
+    d2 = db.covis_distance(poses, g.disps[:2].contiguous(), g.intrinsics, torch.tensor([0], device="cuda"))
+    assert float(d2[0]) >= 100.0
