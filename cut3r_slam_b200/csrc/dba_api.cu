@@ -117,6 +117,7 @@ struct dba_ctx {
   DevBuf d_pt;
   DevBuf d_jd;                 // proj_trans outputs inside dba_jdsa
   DevBuf d_cov;                // L^-1 and S^-1 of dba_depth_cov
+  DevBuf d_slot;               // dba_damping_gather: frame -> eta row
   int pt_M = 0, pt_N = 0;
   bool pt_contig = true;       // unique(ii) is a contiguous range of frames
   // NCCL
@@ -565,7 +566,7 @@ void dba_destroy(dba_ctx* c) {
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
-                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov};
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
@@ -900,6 +901,39 @@ int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const fl
   g_launch_count = 0;
   CK(launch_reproject(poses, disps, intrinsics, ii, jj, int(E), int(N), ht * wd, wd, coords_out, valid_out,
                       reinterpret_cast<cudaStream_t>(stream)), "reproject");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_motion_features(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                        const int64_t* jj, const float* target, int64_t E, int64_t N, int ht, int wd, float* coords_out,
+                        float* valid_out, float* motn_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0) return fail_arg(ctx, "negative or zero size");
+  if (E > 65535) return fail_arg(ctx, "more than 65535 edges in one motion_features call");
+  if (E == 0) return 0;
+  if (!poses || !disps || !intrinsics || !ii || !jj || !target || !coords_out || !valid_out || !motn_out)
+    return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  g_launch_count = 0;
+  CK(launch_motion_features(poses, disps, intrinsics, ii, jj, target, int(E), int(N), ht * wd, wd, coords_out, valid_out,
+                            motn_out, reinterpret_cast<cudaStream_t>(stream)), "motion_features");
+  ctx->last_launches = g_launch_count;
+  return 0;
+}
+
+int dba_damping_gather(dba_ctx* ctx, const float* damping, const int64_t* ii, int64_t E, int64_t N, int ht, int wd,
+                       int64_t M, float* eta_out, void* stream) {
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || M < 0) return fail_arg(ctx, "negative or zero size");
+  if (N > 12000) return fail_arg(ctx, "frame buffer larger than 12000 frames");
+  if (E == 0 || M == 0) return 0;
+  if (!damping || !ii || !eta_out) return fail_arg(ctx, "NULL argument");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  CK(ctx->d_slot.ensure(size_t(N) * sizeof(int32_t) + 16), "slot map");
+  g_launch_count = 0;
+  CK(launch_damping_gather(damping, ii, int(E), int(N), ht * wd, int(M), ctx->d_slot.as<int32_t>(), eta_out,
+                           reinterpret_cast<cudaStream_t>(stream)), "damping_gather");
   ctx->last_launches = g_launch_count;
   return 0;
 }

@@ -44,6 +44,69 @@ k_reproject(const float* __restrict__ poses, const float* __restrict__ disps, co
   }
 }
 
+// reproject + motion features in one pass (FactorGraph.update, factor_graph.pyc update@195-197):
+//   coords1 = reproject(ii, jj);  motn = cat([coords1 - coords0, target - coords1], -1).permute(0,1,4,2,3).clamp(-64, 64)
+// coords0 is the pixel grid.  Outputs: coords [E,HW] float2, valid [E,HW], motn [E,4,HW] (four coalesced planes).
+__global__ void __launch_bounds__(RP_T)
+k_motion_features(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                  const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, const float2* __restrict__ target,
+                  int N, int HW, int wd, float2* __restrict__ coords, float* __restrict__ valid,
+                  float* __restrict__ motn) {
+  __shared__ float sRt[12];
+  const int e = blockIdx.y;
+  const int64_t i64 = ii[e], j64 = jj[e];
+  const bool ok = i64 >= 0 && i64 < N && j64 >= 0 && j64 < N;
+  if (ok && threadIdx.x == 0) relative_pose_Rt(poses, int(i64), int(j64), sRt);
+  __syncthreads();
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const float* dsrc = disps + (ok ? i64 : 0) * HW;
+  for (int p = blockIdx.x * RP_T + threadIdx.x; p < HW; p += gridDim.x * RP_T) {
+    const int py = p / wd, px = p - py * wd;
+    float u = 0.f, v = 0.f, val = 0.f;
+    if (ok) {
+      const Proj pr = project(sRt, (float(px) - cx) / fx, (float(py) - cy) / fy, __ldg(dsrc + p), fx, fy, cx, cy);
+      u = pr.u; v = pr.v; val = pr.valid;
+    }
+    const float2 tg = __ldcs(target + int64_t(e) * HW + p);
+    __stcs(coords + int64_t(e) * HW + p, make_float2(u, v));
+    __stcs(valid + int64_t(e) * HW + p, val);
+    float* mo = motn + int64_t(e) * 4 * HW + p;
+    __stcs(mo, fminf(fmaxf(u - float(px), -64.f), 64.f));
+    __stcs(mo + HW, fminf(fmaxf(v - float(py), -64.f), 64.f));
+    __stcs(mo + 2 * HW, fminf(fmaxf(tg.x - u, -64.f), 64.f));
+    __stcs(mo + 3 * HW, fminf(fmaxf(tg.y - v, -64.f), 64.f));
+  }
+}
+
+// damping of the edges' source keyframes (factor_graph.pyc update@214,227):
+//   eta = 0.2 * damping[unique(ii)] + 1e-7, rows in sorted(unique(ii)) order.
+// One CTA marks the frames that occur in ii and ranks them (slot[f] = row of frame f, -1 if absent) ...
+__global__ void __launch_bounds__(1024)
+k_source_slots(const int64_t* __restrict__ ii, int E, int N, int32_t* __restrict__ slot) {
+  extern __shared__ int sflag[];                  // [N] flags, then an inclusive scan in place
+  for (int f = threadIdx.x; f < N; f += blockDim.x) sflag[f] = 0;
+  __syncthreads();
+  for (int e = threadIdx.x; e < E; e += blockDim.x) {
+    const int64_t f = ii[e];
+    if (f >= 0 && f < N) sflag[f] = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {                         // N is a few hundred to a few thousand: a serial scan is microseconds
+    int run = 0;
+    for (int f = 0; f < N; ++f) { const int fl = sflag[f]; slot[f] = fl ? run : -1; run += fl; }
+  }
+}
+// ... and every marked frame's map is scaled into its row
+__global__ void __launch_bounds__(256)
+k_damping_gather(const float* __restrict__ damping, const int32_t* __restrict__ slot, int HW, int M,
+                 float* __restrict__ eta) {
+  const int f = blockIdx.y;
+  const int r = slot[f];
+  if (r < 0 || r >= M) return;
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  if (p < HW) eta[int64_t(r) * HW + p] = 0.2f * __ldg(damping + int64_t(f) * HW + p) + 1e-7f;
+}
+
 constexpr int UP_T = 256;          // 8 sub-columns j x 32 coarse pixels
 
 // NC channels per pass (1, 2 or 4); channels [c0, c0 + nc) of `dim`
@@ -177,6 +240,26 @@ cudaError_t launch_reproject(const float* poses, const float* disps, const float
   if (nsplit < 1) nsplit = 1;
   dim3 grid(nsplit, E);
   k_reproject<<<grid, RP_T, 0, st>>>(poses, disps, intr, ii, jj, N, HW, wd, reinterpret_cast<float2*>(coords), valid);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_motion_features(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                   const int64_t* jj, const float* target, int E, int N, int HW, int wd, float* coords,
+                                   float* valid, float* motn, cudaStream_t st) {
+  int nsplit = (HW + RP_T * 4 - 1) / (RP_T * 4);
+  if (nsplit < 1) nsplit = 1;
+  k_motion_features<<<dim3(nsplit, E), RP_T, 0, st>>>(poses, disps, intr, ii, jj, reinterpret_cast<const float2*>(target),
+                                                      N, HW, wd, reinterpret_cast<float2*>(coords), valid, motn);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_damping_gather(const float* damping, const int64_t* ii, int E, int N, int HW, int M, int32_t* slot,
+                                  float* eta, cudaStream_t st) {
+  k_source_slots<<<1, 1024, size_t(N) * sizeof(int), st>>>(ii, E, N, slot);
+  g_launch_count++;
+  k_damping_gather<<<dim3((HW + 255) / 256, N), 256, 0, st>>>(damping, slot, HW, M, eta);
   g_launch_count++;
   return cudaGetLastError();
 }

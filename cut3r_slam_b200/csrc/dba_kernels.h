@@ -113,6 +113,11 @@ cudaError_t launch_bi_inter(const float* scales, const float* grid, int M, int H
                             float* J, cudaStream_t st);
 cudaError_t launch_reproject(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                              const int64_t* jj, int E, int N, int HW, int wd, float* coords, float* valid, cudaStream_t st);
+cudaError_t launch_motion_features(const float* poses, const float* disps, const float* intr, const int64_t* ii,
+                                   const int64_t* jj, const float* target, int E, int N, int HW, int wd, float* coords,
+                                   float* valid, float* motn, cudaStream_t st);
+cudaError_t launch_damping_gather(const float* damping, const int64_t* ii, int E, int N, int HW, int M, int32_t* slot,
+                                  float* eta, cudaStream_t st);
 cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int ht, int wd, int dim, float* up,
                                 cudaStream_t st);
 void cholesky_ldiag_layout(int* stride, int* linv_offset);   // per 32-block: where L_kk^-1 (row-major 32x32) sits

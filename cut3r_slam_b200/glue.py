@@ -95,3 +95,51 @@ def add_rel_poses(poses, disps, intrinsics, ii, jj, target, weight):
                                            C.c_void_p(stream)))
     keep = val > 1e-2                                       # pgo_buffer.py:87-89
     return ii[keep], jj[keep], rel[keep], cov[keep], val[keep]
+
+
+def motion_features(poses, disps, intrinsics, ii, jj, target):
+    """The first step of FactorGraph.update (factor_graph.pyc update@195-197) in one launch:
+        coords1, valid = reproject(ii, jj)
+        motn = cat([coords1 - coords0, target - coords1], -1).permute(0, 1, 4, 2, 3).clamp(-64, 64)
+    target [1,E,ht,wd,2] (or [E,ht,wd,2]) -> coords1 [1,E,ht,wd,2], valid [1,E,ht,wd,1], motn [1,E,4,ht,wd]."""
+    _check(poses, "poses", torch.float32, 2)
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    _check(target, "target", torch.float32)
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if jj.numel() != E or target.numel() != E * ht * wd * 2:
+        raise RuntimeError(f"target must hold [{E},{ht},{wd},2] values and jj {E} indices")
+    coords = torch.empty((1, E, ht, wd, 2), dtype=torch.float32, device=poses.device)
+    valid = torch.empty((1, E, ht, wd, 1), dtype=torch.float32, device=poses.device)
+    motn = torch.empty((1, E, 4, ht, wd), dtype=torch.float32, device=poses.device)
+    tg = target.reshape(E, ht, wd, 2)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        for lo in range(0, E, 32768):
+            n = min(32768, E - lo)
+            ctx.check(ctx.lib.dba_motion_features(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics),
+                                                  _ptr(ii[lo:lo + n]), _ptr(jj[lo:lo + n]), _ptr(tg[lo:lo + n]), n, N,
+                                                  ht, wd, _ptr(coords[0, lo:lo + n]), _ptr(valid[0, lo:lo + n]),
+                                                  _ptr(motn[0, lo:lo + n]), C.c_void_p(stream)))
+    return coords, valid, motn
+
+
+def damping_eta(damping, ii):
+    """The `eta` argument of `ba` as FactorGraph.update builds it (factor_graph.pyc update@227):
+    0.2 * damping[unique(ii)] + 1e-7, [M,ht,wd] with rows in sorted(unique(ii)) order.  damping [N,ht,wd]."""
+    from .droid_backends import _num_sources
+    _check(damping, "damping", torch.float32, 3)
+    _check(ii, "ii", torch.int64, 1)
+    N, ht, wd = damping.shape
+    M = _num_sources(ii) if ii.numel() else 0
+    eta = torch.empty((M, ht, wd), dtype=torch.float32, device=damping.device)
+    ctx = context(damping.device)
+    with torch.cuda.device(damping.device):
+        stream = torch.cuda.current_stream(damping.device).cuda_stream
+        ctx.check(ctx.lib.dba_damping_gather(ctx.handle, _ptr(damping), _ptr(ii), ii.numel(), N, ht, wd, M, _ptr(eta),
+                                             C.c_void_p(stream)))
+    return eta

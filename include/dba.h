@@ -151,6 +151,19 @@ int dba_rel_pose_cov(dba_ctx* ctx, const float* poses, const float* disps, const
 int dba_reproject(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
                   const int64_t* jj, int64_t E, int64_t N, int ht, int wd, float* coords_out, float* valid_out,
                   void* stream);
+/* motion features of FactorGraph.update (factor_graph.pyc update@195-197), fused with the reprojection:
+ *   coords1, valid = reproject(ii, jj);  motn = cat([coords1 - coords0, target - coords1], -1).permute(0,1,4,2,3)
+ *   .clamp(-64, 64), coords0 = the pixel grid.  target [E,ht,wd,2] (the previous update's target); outputs coords
+ *   [E,ht,wd,2], valid [E,ht,wd,1], motn [E,4,ht,wd].  Bytecode-only in the reference tree -> parity unpinned
+ *   (restated in oracle/glue.py from the disassembly and upstream DROID-SLAM's two torch lines). */
+int dba_motion_features(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                        const int64_t* jj, const float* target, int64_t E, int64_t N, int ht, int wd, float* coords_out,
+                        float* valid_out, float* motn_out, void* stream);
+/* damping gather of FactorGraph.update (factor_graph.pyc update@227): eta [M,ht,wd] = 0.2 * damping[unique(ii)] + 1e-7,
+ *   rows in sorted(unique(ii)) order -- the `eta` argument of dba_ba.  damping [N,ht,wd]; M = |unique(ii)| (the
+ *   caller knows it: it sizes eta); unique / rank are computed on the device, no host round trip. */
+int dba_damping_gather(dba_ctx* ctx, const float* damping, const int64_t* ii, int64_t E, int64_t N, int ht, int wd,
+                       int64_t M, float* eta_out, void* stream);
 /* cvx_upsample(data, mask) -> up  [hislam2/modules/droid_net.py:21-38; upsample_disp :40-44 is dim = 1]:
  *   data [B,ht,wd,dim], mask [B,576,ht,wd] (= [B,9,8,8,ht,wd] logits), up [B,8ht,8wd,dim].  `mask` is read-only
  *   here (the reference writes -inf into the border entries of the caller's tensor as a side effect). */

@@ -51,3 +51,20 @@ def upsample_disp(disp, mask):
     B, num, ht, wd = disp.shape
     up = cvx_upsample(disp.reshape(B * num, ht, wd, 1), mask.reshape(B * num, -1, ht, wd))
     return up.reshape(B, num, 8 * ht, 8 * wd)
+
+
+def motion_features(poses, disps, intrinsics, ii, jj, target):
+    """factor_graph.pyc update@195-197 (bytecode only in the reference tree; upstream DROID-SLAM factor_graph.py:
+    `motn = torch.cat([coords1 - self.coords0, self.target - coords1], dim=-1); motn = motn.permute(0,1,4,2,3)
+    .clamp(-64.0, 64.0)`): target [E,ht,wd,2] -> coords1 [E,ht,wd,2], valid [E,ht,wd,1], motn [E,4,ht,wd]."""
+    coords1, valid = od.projective_transform(poses, disps, intrinsics, ii, jj)
+    ht, wd = disps.shape[-2:]
+    y, x = torch.meshgrid(torch.arange(ht, dtype=poses.dtype), torch.arange(wd, dtype=poses.dtype), indexing="ij")
+    coords0 = torch.stack([x, y], dim=-1)
+    motn = torch.cat([coords1 - coords0, target - coords1], dim=-1).permute(0, 3, 1, 2).clamp(-64.0, 64.0)
+    return coords1, valid, motn
+
+
+def damping_eta(damping, ii):
+    """factor_graph.pyc update@227: 0.2 * self.damping[torch.unique(ii)].contiguous() + EP with EP = 1e-7."""
+    return 0.2 * damping[torch.unique(ii)] + 1e-7

@@ -102,3 +102,29 @@ def test_reproject_backend_size_matches_oracle():
     bad = torch.tensor([0, 10 ** 6, -1], device="cuda")
     c, v = gl.reproject(g.poses, g.disps, g.intrinsics, torch.zeros(3, dtype=torch.long, device="cuda"), bad)
     assert float(v[0, 0].min()) == 1.0 and float(v[0, 1:].abs().max()) == 0.0 and float(c[0, 1:].abs().max()) == 0.0
+
+
+def test_motion_features_and_damping_gather():
+    """The two remaining elementwise steps of FactorGraph.update (factor_graph.pyc update@195-197, @227) against
+    their torch restatement (bytecode only in the reference tree: parity unpinned)."""
+    import oracle.glue as og
+    from cut3r_slam_b200 import glue
+    from cut3r_slam_b200.synthetic import make_problem
+    p = make_problem("frontend")
+    g = p.to("cuda")
+    target = p.targets.permute(0, 2, 3, 1).contiguous()                   # the reference's [E,ht,wd,2] layout
+    c_ref, v_ref, m_ref = og.motion_features(p.poses.double(), p.disps.double(), p.intrinsics.double(), p.ii, p.jj,
+                                             target.double())
+    coords, valid, motn = glue.motion_features(g.poses, g.disps, g.intrinsics, g.ii, g.jj, target.cuda()[None])
+    assert coords.shape == (1,) + tuple(c_ref.shape) and motn.shape == (1,) + tuple(m_ref.shape)
+    assert float((coords[0].cpu().double() - c_ref).abs().max()) < 2e-3        # pixels, fp32 vs fp64
+    assert torch.equal(valid[0].cpu().double(), v_ref)
+    assert float((motn[0].cpu().double() - m_ref).abs().max()) < 2e-3
+    assert float(motn.abs().max()) <= 64.0
+    # damping: frames 3 and 7 are not sources -> rows follow sorted(unique(ii))
+    keep = (p.ii != 3) & (p.ii != 7)
+    ii = p.ii[keep].cuda()
+    damping = torch.rand(p.disps.shape, generator=torch.Generator().manual_seed(3)) * 1e-3
+    eta = glue.damping_eta(damping.cuda(), ii)
+    ref = og.damping_eta(damping, p.ii[keep])
+    assert eta.shape == ref.shape and torch.equal(eta.cpu(), ref)
