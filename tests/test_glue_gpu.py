@@ -127,4 +127,4 @@ def test_motion_features_and_damping_gather():
     damping = torch.rand(p.disps.shape, generator=torch.Generator().manual_seed(3)) * 1e-3
     eta = glue.damping_eta(damping.cuda(), ii)
     ref = og.damping_eta(damping, p.ii[keep])
-    assert eta.shape == ref.shape and torch.equal(eta.cpu(), ref)
+    assert eta.shape == ref.shape and float((eta.cpu() - ref).abs().max()) < 1e-9        # 0.2 d + 1e-7: FMA vs mul, add
