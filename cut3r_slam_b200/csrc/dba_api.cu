@@ -105,6 +105,8 @@ struct dba_ctx {
   bool opt_v2 = true;                // narrow keyframes on the one-warp-per-edge kernel (dba_linearize_v2.cu)
   bool plan_v2 = false;              // ... and the cached plan was split for it
   int opt_wide_tc = 2;               // 0: SIMT above out-degree 20; 1: WIDE tcgen05 variant up to 25; 2: up to 41          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
+  int opt_chol_tc = 1;               // 0 off; 1: n >= cholesky_tc_min_n() on 128-column panels + tcgen05 trailing update;
+                                     // > 1: from that n on (tests)
   int opt_refine = 1;                // iterative refinement of the pose solve: 0 off, 1 auto, 2 every iteration
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows
   // host staging
@@ -485,7 +487,10 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     if (ctx->opt_small && g.n6 <= cholesky_small_max_n())
       CK(launch_cholesky_small(ws, g.n6, st), "cholesky (single CTA)");
     else if (ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol) {
-      CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st, !refine), "cholesky (cooperative)");
+      if (ctx->opt_chol_tc != 0 && g.n6 >= (ctx->opt_chol_tc > 1 ? ctx->opt_chol_tc : cholesky_tc_min_n()))
+        CK(launch_cholesky_tc(ws, g.n6, st, !refine), "cholesky (tcgen05 panels)");
+      else
+        CK(launch_cholesky_coop(ws, g.n6, ctx->coop_ctas, st, !refine), "cholesky (cooperative)");
       if (refine) CK(launch_refine(ws, ctx->Akeep.as<float>(), g.n6, st), "refinement");
     }
     else
@@ -592,6 +597,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = int(value); ctx->plan_valid = false; }
   else if (n == "small_system") ctx->opt_small = value != 0;
   else if (n == "refine") ctx->opt_refine = int(value);
+  else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {

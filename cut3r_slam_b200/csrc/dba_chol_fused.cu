@@ -20,6 +20,7 @@
 // then y -= L_k.^T x_k with the rows of L fetched while the warp works.
 // A non-positive / NaN pivot raises the flag -> dx = 0 (chol.py:14-18 behaviour).
 #include "dba_kernels.h"
+#include "dba_umma.cuh"
 
 namespace dba {
 
@@ -625,6 +626,40 @@ k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx
 }
 
 }  // namespace
+
+#include "dba_chol_tc.cuh"
+
+// Factorisation + forward solve of the rhs row with 128-column panels (dba_chol_tc.cuh), then the backward solve.
+// 3 launches per panel; all on `st`.
+cudaError_t launch_cholesky_tc(const Workspace& ws, int n, cudaStream_t st, bool finalize) {
+  static bool attr_done = false;
+  const size_t smem_p = potrf128_smem_floats() * sizeof(float);
+  const size_t smem_t = (size_t(PW) * PW + PW + size_t(PW) * 128) * sizeof(float);
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(k_potrf128, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_p));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm128, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_t));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_syrk_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SY_SMEM));
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  for (int k0 = 0; k0 < n; k0 += PW) {
+    const int w = (n - k0 < PW) ? n - k0 : PW, r0 = k0 + w;
+    k_potrf128<<<1, 256, smem_p, st>>>(ws.A, ws.Lm, ws.Ldiag, ws.ldA, n, k0, ws.fail);
+    k_trsm128<<<(n + 1 - r0 + 127) / 128, 128, smem_t, st>>>(ws.A, ws.Lm, ws.ldA, n, k0);
+    g_launch_count += 2;
+    if (r0 < n) {
+      const int ntj = (n - r0 + PW - 1) / PW, nti = (n + 1 - r0 + PW - 1) / PW;
+      const int ntiles = ntj * (ntj + 1) / 2 + (nti > ntj ? ntj : 0);
+      k_syrk_tc<<<ntiles, SY_T, SY_SMEM, st>>>(ws.A, ws.Lm, ws.ldA, n, k0);
+      g_launch_count++;
+    }
+  }
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return err;
+  return launch_backsolve(ws, n, finalize ? 1 : 0, st);
+}
+
+int cholesky_tc_min_n() { return 1024; }
 
 #ifdef DBA_CHOL_TRACE
 void chol_trace_read(unsigned long long* out, int n) { cudaMemcpyFromSymbol(out, g_trace, sizeof(unsigned long long) * n); }

@@ -82,6 +82,9 @@ int cholesky_small_max_n();
 cudaError_t launch_cholesky_solve(const Workspace& ws, int n6, cudaStream_t st);
 // single cooperative launch (one grid barrier per block step); max_ctas from cholesky_coop_max_ctas (0 = unavailable)
 cudaError_t launch_cholesky_coop(const Workspace& ws, int n6, int max_ctas, cudaStream_t st, bool finalize = true);
+// large systems (n >= cholesky_tc_min_n()): 128-column panels, trailing update on tcgen05 (dba_chol_tc.cuh)
+cudaError_t launch_cholesky_tc(const Workspace& ws, int n6, cudaStream_t st, bool finalize = true);
+int cholesky_tc_min_n();
 cudaError_t launch_backsolve(const Workspace& ws, int n6, int mode, cudaStream_t st);
 // one step of iterative refinement after launch_cholesky_coop(..., finalize = false): r = rhs - S dx accumulated in fp64
 // from the saved system Sorig [(n6+1), ldA] (lower + rhs row), L y = r, L^T d = y, dx += d  (dba_refine.cu)

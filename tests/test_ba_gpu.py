@@ -323,3 +323,26 @@ def test_wide_tensor_core_keyframes(level, P, r, E):
     assert rel_err(disps, disps64) < 1e-4
     assert rel_err(dxs[0], simt_dx[0]) < MULT * gap + 1e-5
     assert rel_err(disps, simt_disps) < 1e-4          # two summation orders, each within the bar above
+
+
+@pytest.mark.parametrize("P,E", [(40, 300), (60, 500)])
+def test_tensor_core_cholesky_agrees(P, E):
+    """The 128-column-panel factorisation with the tcgen05 trailing update (default from n = 1024) forced on small
+    systems: n = 228 (one full panel + a 100-wide one) and n = 348 (two full panels + 92), against the cooperative
+    kernel and the fp64 oracle.  Refinement off so that the factorisations themselves are compared."""
+    db = _db()
+    p = make_problem(P=P, E=E, ht=20, wd=24, iters=2, t0=2, r=4, seed=81)
+    db.set_option("refine", 0)
+    try:
+        a = p.to("cuda")
+        db.ba(*a.ba_args())
+        db.set_option("cholesky_tc", 64)
+        b = p.to("cuda")
+        db.ba(*b.ba_args())
+    finally:
+        db.set_option("cholesky_tc", 1)
+        db.set_option("refine", 1)
+    assert rel_err(b.disps.cpu(), a.disps.cpu()) < 2e-4
+    assert float((b.poses - a.poses).abs().max()) < 1e-4
+    ref_p, ref_d = od.oracle_ba(*p.ba_args(), dtype=torch.float64)
+    assert rel_err(b.disps.cpu(), ref_d) < 1e-4
