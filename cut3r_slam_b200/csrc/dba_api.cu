@@ -105,7 +105,7 @@ struct dba_ctx {
   bool opt_v2 = true;                // narrow keyframes on the one-warp-per-edge kernel (dba_linearize_v2.cu)
   bool plan_v2 = false;              // ... and the cached plan was split for it
   int opt_wide_tc = 2;               // 0: SIMT above out-degree 20; 1: WIDE tcgen05 variant up to 25; 2: up to 41          // out-degree 21..25 on the WIDE tcgen05 variant instead of the SIMT kernel
-  int opt_chol_tc = 1;               // 0 off; 1: n >= cholesky_tc_min_n() on 128-column panels + tcgen05 trailing update;
+  int opt_chol_tc = 0;               // 0 off (default: measured slower, profiles/r2_cholesky_tc.md); 1: n >= cholesky_tc_min_n() on 128-column panels + tcgen05 trailing update;
                                      // > 1: from that n on (tests)
   int opt_refine = 1;                // iterative refinement of the pose solve: 0 off, 1 auto, 2 every iteration
   bool opt_small = true;             // single-CTA solve for n6 <= small_system_max_n()                // Schur products on tcgen05 where the out-degree allows

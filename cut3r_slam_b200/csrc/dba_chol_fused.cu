@@ -634,23 +634,23 @@ k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx
 cudaError_t launch_cholesky_tc(const Workspace& ws, int n, cudaStream_t st, bool finalize) {
   static bool attr_done = false;
   const size_t smem_p = potrf128_smem_floats() * sizeof(float);
-  const size_t smem_t = (size_t(PW) * PW + PW + size_t(PW) * 128) * sizeof(float);
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(k_potrf128, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_p));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm128, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_t));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_syrk_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SY_SMEM));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_syrk_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SY_SMEM));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_syrk_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(SY_SMEM));
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
+  float* LinvW = ws.Ldiag + size_t((n + NB - 1) / NB) * LD_STRIDE;      // [128][128] behind the per-block entries
   for (int k0 = 0; k0 < n; k0 += PW) {
     const int w = (n - k0 < PW) ? n - k0 : PW, r0 = k0 + w;
-    k_potrf128<<<1, 256, smem_p, st>>>(ws.A, ws.Lm, ws.Ldiag, ws.ldA, n, k0, ws.fail);
-    k_trsm128<<<(n + 1 - r0 + 127) / 128, 128, smem_t, st>>>(ws.A, ws.Lm, ws.ldA, n, k0);
+    k_potrf128<<<1, 256, smem_p, st>>>(ws.A, ws.Lm, ws.Ldiag, LinvW, ws.ldA, n, k0, ws.fail);
+    k_syrk_tc<1><<<(n + 1 - r0 + PW - 1) / PW, SY_T, SY_SMEM, st>>>(ws.A, ws.Lm, LinvW, ws.ldA, n, k0);
     g_launch_count += 2;
     if (r0 < n) {
       const int ntj = (n - r0 + PW - 1) / PW, nti = (n + 1 - r0 + PW - 1) / PW;
       const int ntiles = ntj * (ntj + 1) / 2 + (nti > ntj ? ntj : 0);
-      k_syrk_tc<<<ntiles, SY_T, SY_SMEM, st>>>(ws.A, ws.Lm, ws.ldA, n, k0);
+      k_syrk_tc<0><<<ntiles, SY_T, SY_SMEM, st>>>(ws.A, ws.Lm, LinvW, ws.ldA, n, k0);
       g_launch_count++;
     }
   }
@@ -714,7 +714,7 @@ cudaError_t launch_cholesky_small(const Workspace& ws, int n, cudaStream_t st) {
   return cudaGetLastError();
 }
 
-size_t cholesky_ldiag_floats(int n) { return size_t((n + NB - 1) / NB) * LD_STRIDE; }
+size_t cholesky_ldiag_floats(int n) { return size_t((n + NB - 1) / NB) * LD_STRIDE + size_t(PW) * PW; }
 void cholesky_ldiag_layout(int* stride, int* linv_offset) { *stride = LD_STRIDE; *linv_offset = LD_LINV; }
 
 int cholesky_coop_max_ctas(int n) {

@@ -8,9 +8,10 @@
 //   k_potrf128 : one CTA factors the 128 x 128 diagonal block in shared memory (four 32-column sub-steps: register
 //                potrf in one warp, one thread per row for the rows below, SIMT update of the rest of the block) and
 //                publishes L_kk plus the per-32-block L^T, 1/diag, L^-1 the triangular solves use;
-//   k_trsm128  : X = A[rows below, panel] L_kk^-T by forward substitution, one thread per matrix row (the rhs row n
-//                rides along as a matrix row: the forward solve falls out of the factorisation as before);
-//   k_syrk_tc  : C -= X_i X_j^T on 128 x 128 tiles: the fp32 panel rows are split into tf32 (hi, lo) pairs while
+//   k_syrk_tc<1>: X = A[rows below, panel] L_kk^-T as a tensor-core product with the explicit inverse of the diagonal
+//                block (the rhs row n rides along as a matrix row: the forward solve falls out of the factorisation);
+//                a first version with one thread per row doing the substitution took 80 us per panel
+//   k_syrk_tc<0>: C -= X_i X_j^T on 128 x 128 tiles: the fp32 panel rows are split into tf32 (hi, lo) pairs while
 //                they are copied into the SWIZZLE_128B K-major operand tiles, tcgen05.mma accumulates
 //                hi lo^T + lo hi^T + hi hi^T over the 128 panel columns in TMEM ("3xTF32", two K-halves of 64),
 //                the result is subtracted from the tile in global memory (L2 resident).
@@ -24,20 +25,22 @@ using namespace umma;
 constexpr int PW = 128;              // panel width
 constexpr int PLD = PW + 4;          // row stride of the diagonal block in shared memory
 
-// dynamic shared memory of k_potrf128: sA [PW][PLD] | LT [32][32] | rinv [32] | Pp [32][PW] | col [2][32]
-__host__ __device__ inline size_t potrf128_smem_floats() { return size_t(PW) * PLD + 32 * 32 + 32 + 32 * PW + 64; }
+// dynamic shared memory of k_potrf128: sA [PW][PLD] | LT [32][32] | rinv [32] | Pp [32][PW] | col [2][32] | sLi [PW][PLD]
+__host__ __device__ inline size_t potrf128_smem_floats() { return 2 * size_t(PW) * PLD + 32 * 32 + 32 + 32 * PW + 64; }
 
 __global__ void __launch_bounds__(256)
-k_potrf128(const float* __restrict__ A, float* __restrict__ Lm, float* __restrict__ Ldiag, int ld, int n, int k0,
-           int* __restrict__ fail) {
+k_potrf128(const float* __restrict__ A, float* __restrict__ Lm, float* __restrict__ Ldiag, float* __restrict__ LinvW,
+           int ld, int n, int k0, int* __restrict__ fail) {
   extern __shared__ __align__(16) float psm[];
   float* sA = psm;                                   // the diagonal block, lower triangle
   float (*LT)[NB] = reinterpret_cast<float (*)[NB]>(sA + PW * PLD);   // LT[j][c] = L[c][j] of the current 32-block
   float* rinv = sA + PW * PLD + NB * NB;
   float* Pp = rinv + NB;                             // [32][PW]: solved rows below the 32-block, k-major
   float* col = Pp + NB * PW;
+  float* sLi = col + 64;                             // [PW][PLD]: L_kk^-1 (lower), built from the 32-block inverses
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int w = min(PW, n - k0);
+  for (int e = tid; e < PW * PLD; e += 256) sLi[e] = 0.f;
   for (int e = tid; e < PW * (PW / 4); e += 256) {   // 128 rows x 32 float4 chunks
     const int i = e >> 5, c4 = (e & 31) * 4;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -84,89 +87,79 @@ k_potrf128(const float* __restrict__ A, float* __restrict__ Lm, float* __restric
       for (int c = 0; c < NB; ++c) b[c] = (c == lane) ? 1.f : 0.f;
       solve_row(b, LT, rinv);
 #pragma unroll
-      for (int j = 0; j < NB; ++j) Lg[LD_LINV + j * NB + lane] = b[j];
+      for (int j = 0; j < NB; ++j) { Lg[LD_LINV + j * NB + lane] = b[j]; sLi[(s0 + j) * PLD + s0 + lane] = b[j]; }
     }
     __syncthreads();
-    for (int e = tid; e < nrow * nrow; e += 256) {   // ---- rest of the block: lower part only
-      const int ri = e / nrow, rc = e - ri * nrow;
-      if (rc <= ri) {
-        float acc = 0.f;
+    {  // ---- rest of the block (lower part), 4 x 4 register tiles: tile (ty, tx <= ty) of the nrow x nrow remainder
+      const int nt4 = (nrow + 3) >> 2;
+      for (int t = tid; t < nt4 * nt4; t += 256) {
+        const int ty = t / nt4, tx = t - ty * nt4;
+        if (tx > ty) continue;
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 #pragma unroll 8
-        for (int m = 0; m < NB; ++m) acc = fmaf(Pp[m * PW + ri], Pp[m * PW + rc], acc);
-        sA[(r0 + ri) * PLD + r0 + rc] -= acc;
+        for (int m = 0; m < NB; ++m) {
+          const float4 a4 = *reinterpret_cast<const float4*>(Pp + m * PW + 4 * ty);
+          const float4 b4 = *reinterpret_cast<const float4*>(Pp + m * PW + 4 * tx);
+          const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int ri = 4 * ty + i, rc = 4 * tx + j;
+            if (ri < nrow && rc <= ri) sA[(r0 + ri) * PLD + r0 + rc] -= acc[i][j];
+          }
       }
     }
     __syncthreads();
+  }
+  // ---- the full inverse of the 128 x 128 factor from its 32-block inverses (k_trsm as a tensor-core product):
+  // column block j, rows i > j in turn:  Linv_ij = -Linv_ii (sum_{k=j}^{i-1} L_ik Linv_kj);  Pp holds the sum
+  for (int j = 0; j + 1 < nsb; ++j)
+    for (int i = j + 1; i < nsb; ++i) {
+      {
+        const int r = tid >> 3, c4 = (tid & 7) * 4;   // thread -> row r of the 32 x 32 block, 4 columns
+        float t4[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = j; k < i; ++k)
+#pragma unroll 8
+          for (int m = 0; m < NB; ++m) {
+            const float l = sA[(i * NB + r) * PLD + k * NB + m];
+            const float4 v = *reinterpret_cast<const float4*>(sLi + (k * NB + m) * PLD + j * NB + c4);
+            t4[0] = fmaf(l, v.x, t4[0]); t4[1] = fmaf(l, v.y, t4[1]); t4[2] = fmaf(l, v.z, t4[2]); t4[3] = fmaf(l, v.w, t4[3]);
+          }
+        *reinterpret_cast<float4*>(Pp + r * PW + c4) = make_float4(t4[0], t4[1], t4[2], t4[3]);
+      }
+      __syncthreads();
+      {
+        const int r = tid >> 3, c4 = (tid & 7) * 4;
+        float t4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+        for (int m = 0; m < NB; ++m) {
+          const float l = sLi[(i * NB + r) * PLD + i * NB + m];
+          const float4 v = *reinterpret_cast<const float4*>(Pp + m * PW + c4);
+          t4[0] = fmaf(l, v.x, t4[0]); t4[1] = fmaf(l, v.y, t4[1]); t4[2] = fmaf(l, v.z, t4[2]); t4[3] = fmaf(l, v.w, t4[3]);
+        }
+        *reinterpret_cast<float4*>(sLi + (i * NB + r) * PLD + j * NB + c4) = make_float4(-t4[0], -t4[1], -t4[2], -t4[3]);
+      }
+      __syncthreads();
+    }
+  for (int e = tid; e < PW * (PW / 4); e += 256) {   // L_kk^-1, rows / columns >= w zero
+    const int i = e >> 5, c4 = (e & 31) * 4;
+    float4 v = *reinterpret_cast<const float4*>(sLi + i * PLD + c4);
+    if (i >= w) v = make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(LinvW + i * PW + c4) = v;
   }
   for (int e = tid; e < w * (PW / 4); e += 256) {    // the factor's diagonal block (lower; the rest is never read)
     const int i = e >> 5, c4 = (e & 31) * 4;
     if (c4 <= i) *reinterpret_cast<float4*>(Lm + int64_t(k0 + i) * ld + k0 + c4) = *reinterpret_cast<const float4*>(sA + i * PLD + c4);
-  }
-}
-
-// X = A[row, k0..k0+w) L_kk^-T for the rows r0..n (n = the rhs row), one thread per row, written to Lm
-__global__ void __launch_bounds__(128)
-k_trsm128(const float* __restrict__ A, float* __restrict__ Lm, int ld, int n, int k0) {
-  extern __shared__ __align__(16) float tsm[];
-  float* LTs = tsm;                                  // [PW][PW]: LTs[j * PW + c] = L[c][j], identity padded
-  float* rinvs = tsm + PW * PW;
-  const int tid = threadIdx.x;
-  const int w = min(PW, n - k0), r0 = k0 + w;
-  for (int e = tid; e < PW * PW; e += 128) {
-    const int c = e >> 7, j = e & 127;               // coalesced read of row c of L
-    float v = (c == j) ? 1.f : 0.f;
-    if (c < w && j < w) v = (j <= c) ? __ldcg(Lm + int64_t(k0 + c) * ld + k0 + j) : 0.f;
-    LTs[j * PW + c] = v;
-  }
-  __syncthreads();
-  rinvs[tid] = 1.0f / LTs[tid * PW + tid];
-  __syncthreads();
-  float* xs = rinvs + PW;                            // [PW][128]: solved entries x_j of the CTA's rows, xs[j * 128 + tid]
-  const int row = r0 + blockIdx.x * 128 + tid;
-  const bool live = row <= n;
-  for (int blk = 0; blk < (w + NB - 1) / NB; ++blk) {
-    const int c0 = blk * NB;
-    float b[NB];
-#pragma unroll
-    for (int c4 = 0; c4 < NB; c4 += 4) {
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (live && c0 + c4 < w) v = __ldcg(reinterpret_cast<const float4*>(A + int64_t(row) * ld + k0 + c0 + c4));
-      b[c4] = v.x; b[c4 + 1] = (c0 + c4 + 1 < w) ? v.y : 0.f; b[c4 + 2] = (c0 + c4 + 2 < w) ? v.z : 0.f;
-      b[c4 + 3] = (c0 + c4 + 3 < w) ? v.w : 0.f;
-    }
-    for (int j = 0; j < c0; ++j) {                   // columns solved in earlier blocks: b -= x_j L[c0.., j]
-      const float x = xs[j * 128 + tid];
-      const float* lj = LTs + j * PW + c0;
-#pragma unroll
-      for (int g = 0; g < NB / 4; ++g) {
-        const float4 l4 = *reinterpret_cast<const float4*>(lj + 4 * g);             // broadcast
-        b[4 * g] = fmaf(-x, l4.x, b[4 * g]);         b[4 * g + 1] = fmaf(-x, l4.y, b[4 * g + 1]);
-        b[4 * g + 2] = fmaf(-x, l4.z, b[4 * g + 2]); b[4 * g + 3] = fmaf(-x, l4.w, b[4 * g + 3]);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < NB; ++j) {                   // the block's own triangle
-      const float x = b[j] * rinvs[c0 + j];
-      b[j] = x;
-      const float* lj = LTs + (c0 + j) * PW + c0;
-#pragma unroll
-      for (int g = (j + 1) / 4; g < NB / 4; ++g) {
-        const float4 l4 = *reinterpret_cast<const float4*>(lj + 4 * g);
-        const int c4 = g * 4;
-        if (c4 + 0 > j) b[c4 + 0] = fmaf(-x, l4.x, b[c4 + 0]);
-        if (c4 + 1 > j) b[c4 + 1] = fmaf(-x, l4.y, b[c4 + 1]);
-        if (c4 + 2 > j) b[c4 + 2] = fmaf(-x, l4.z, b[c4 + 2]);
-        if (c4 + 3 > j) b[c4 + 3] = fmaf(-x, l4.w, b[c4 + 3]);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < NB; ++j) xs[(c0 + j) * 128 + tid] = b[j];
-    if (live) {
-#pragma unroll
-      for (int c4 = 0; c4 < NB; c4 += 4)
-        if (c0 + c4 < w)
-          *reinterpret_cast<float4*>(Lm + int64_t(row) * ld + k0 + c0 + c4) = make_float4(b[c4], b[c4 + 1], b[c4 + 2], b[c4 + 3]);
-    }
   }
 }
 
@@ -182,7 +175,7 @@ constexpr size_t SY_SMEM = 4 * 2 * SY_TILE + 64;
 // rows [row0, row0 + 128) x panel columns [kc, kc + 64) of X (in Lm) -> tf32 (hi, lo) operand tiles
 __device__ __forceinline__ void syrk_stage(const float* __restrict__ Lm, int ld, int row0, int row_max, int k0, int kc,
                                            int w, uint8_t* hi, uint8_t* lo, int tid) {
-#pragma unroll 4
+#pragma unroll 8
   for (int e = tid; e < 128 * 16; e += SY_T) {       // 128 rows x 16 chunks of 4 columns
     const int r = e >> 4, c16 = e & 15;
     const int row = row0 + r, kk = kc + 4 * c16;
@@ -200,19 +193,23 @@ __device__ __forceinline__ void syrk_stage(const float* __restrict__ Lm, int ld,
   }
 }
 
-// C[ti, tj] -= X_i X_j^T for the lower tiles of the trailing matrix (rows r0..n incl. the rhs row, columns r0..n-1)
+// MODE 0: C[ti, tj] -= X_i X_j^T for the lower tiles of the trailing matrix (rows r0..n incl. the rhs row, columns
+//         r0..n-1); X = the solved panel in Lm.
+// MODE 1: the panel solve as a product with the inverse of the diagonal block: X[rows r0..n] = A[rows, panel] L_kk^-T,
+//         written to Lm (one CTA per 128 rows; LinvW [128][128] from k_potrf128).
+template <int MODE>
 __global__ void __launch_bounds__(SY_T, 1)
-k_syrk_tc(float* __restrict__ A, const float* __restrict__ Lm, int ld, int n, int k0) {
+k_syrk_tc(float* __restrict__ A, float* __restrict__ Lm, const float* __restrict__ LinvW, int ld, int n, int k0) {
   extern __shared__ __align__(1024) uint8_t ssm[];
   uint8_t* Ahi = ssm; uint8_t* Alo = ssm + 2 * SY_TILE; uint8_t* Bhi = ssm + 4 * SY_TILE; uint8_t* Blo = ssm + 6 * SY_TILE;
   uint64_t* mbar = reinterpret_cast<uint64_t*>(ssm + 8 * SY_TILE);
   uint32_t* tmem_p = reinterpret_cast<uint32_t*>(mbar + 1);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int w = min(PW, n - k0), r0 = k0 + w;
-  int ti, tj;
-  tri_decode(blockIdx.x, ti, tj);
-  const int rowi = r0 + ti * PW, rowj = r0 + tj * PW;
-  const bool diag = ti == tj;
+  int ti = blockIdx.x, tj = 0;
+  if (MODE == 0) tri_decode(blockIdx.x, ti, tj);
+  const int rowi = r0 + ti * PW, rowj = (MODE == 0) ? r0 + tj * PW : 0;
+  const bool diag = MODE == 0 && ti == tj;
   if ((smem_u32(ssm) & 1023u) != 0u) __trap();
   if (warp == 0) tmem_alloc(tmem_p, 128);
   if (tid == 0) mbar_init(mbar, 1);
@@ -228,8 +225,13 @@ k_syrk_tc(float* __restrict__ A, const float* __restrict__ Lm, int ld, int n, in
       phase ^= 1;
       tc_fence_after_sync();
     }
-    syrk_stage(Lm, ld, rowi, n, k0, kc, w, Ahi, Alo, tid);
-    if (!diag) syrk_stage(Lm, ld, rowj, n - 1, k0, kc, w, Bhi, Blo, tid);
+    if (MODE == 0) {
+      syrk_stage(Lm, ld, rowi, n, k0, kc, w, Ahi, Alo, tid);
+      if (!diag) syrk_stage(Lm, ld, rowj, n - 1, k0, kc, w, Bhi, Blo, tid);
+    } else {
+      syrk_stage(A, ld, rowi, n, k0, kc, w, Ahi, Alo, tid);
+      syrk_stage(LinvW, PW, 0, w - 1, 0, kc, w, Bhi, Blo, tid);
+    }
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
@@ -271,13 +273,19 @@ k_syrk_tc(float* __restrict__ A, const float* __restrict__ Lm, int ld, int n, in
 #pragma unroll
         for (int c4 = 0; c4 < 16; c4 += 4) {
           const int col = gj + c4;
-          // columns past the diagonal of a diagonal tile hold symmetric values nobody reads; columns >= n do not exist
-          if (col < n && col <= gi) {
-            float4* p = reinterpret_cast<float4*>(A + int64_t(gi) * ld + col);
-            float4 c = __ldcg(p);
-            c.x -= __uint_as_float(v[c4]); c.y -= __uint_as_float(v[c4 + 1]);
-            c.z -= __uint_as_float(v[c4 + 2]); c.w -= __uint_as_float(v[c4 + 3]);
-            __stcg(p, c);
+          if (MODE == 0) {
+            // columns past the diagonal of a diagonal tile hold symmetric values nobody reads; columns >= n do not exist
+            if (col < n && col <= gi) {
+              float4* p = reinterpret_cast<float4*>(A + int64_t(gi) * ld + col);
+              float4 c = __ldcg(p);
+              c.x -= __uint_as_float(v[c4]); c.y -= __uint_as_float(v[c4 + 1]);
+              c.z -= __uint_as_float(v[c4 + 2]); c.w -= __uint_as_float(v[c4 + 3]);
+              __stcg(p, c);
+            }
+          } else if (col < w) {
+            __stcg(reinterpret_cast<float4*>(Lm + int64_t(gi) * ld + k0 + col),
+                   make_float4(__uint_as_float(v[c4]), __uint_as_float(v[c4 + 1]), __uint_as_float(v[c4 + 2]),
+                               __uint_as_float(v[c4 + 3])));
           }
         }
       }
