@@ -23,9 +23,10 @@ def partition_by_source(ii, nranks, cost="schur"):
     ii = ii.cpu()
     kx, kk = torch.unique(ii, return_inverse=True)
     deg = torch.bincount(kk, minlength=kx.numel()).double()
-    # measured kernel costs per pixel tile (csrc/dba_api.cu prepare_plan): tcgen05 path deg + 6 up to out-degree
-    # 20, SIMT path 0.064 (deg+1)^2 on a whole SM (two CTA slots) beyond
-    w = torch.where(deg <= 20, deg + 6, 0.128 * (deg + 1) ** 2) if cost == "schur" else deg
+    # measured kernel costs per 64-pixel tile (csrc/dba_api.cu prepare_plan, profiles/r2_linearize_v2.md): the
+    # one-warp-per-edge kernel up to out-degree 20 (the tile time hardly depends on the degree), the WIDE tcgen05
+    # variants beyond (one CTA per SM each, ~0.1 (deg + 1) of a narrow tile)
+    w = torch.where(deg <= 20, 1.0 + 0.03 * deg, 0.1 * (deg + 1)) if cost == "schur" else deg
     cum = torch.cumsum(w, 0)
     total = float(cum[-1]) if cum.numel() else 0.0
     bounds = [0]
