@@ -56,6 +56,8 @@ SIGNATURES = {
     "dba_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "dba_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "dba_comm_destroy": (C.c_int, [C.c_void_p]),
+    "dba_comm_p2p_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "dba_comm_p2p_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "dba_debug_read": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64]),
     "dba_last_launch_count": (C.c_int64, [C.c_void_p]),
     "dba_plan_build": (C.c_void_p, [c_i, c_i, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,

@@ -125,6 +125,14 @@ struct dba_ctx {
   // NCCL
   void* comm = nullptr;
   int nranks = 1, rank = 0;
+  // one-shot all-reduce over peer memory (dba_p2p.cu): exchange buffer = 2 slabs + flags, mapped by every rank
+  float* p2p_buf = nullptr;
+  size_t p2p_slab_floats = 0;
+  P2PPeers p2p_peers{};
+  bool p2p_ok = false;
+  bool opt_p2p = true;
+  int opt_p2p_max_n = 1536;          // larger systems are bandwidth-bound: NCCL's reduce-scatter + all-gather moves less
+  uint32_t p2p_epoch = 0;
   int64_t last_launches = 0;
   size_t smem_cap = 0;
 };
@@ -454,9 +462,24 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       }
     }
     mark();
+    const bool sharded = ctx->comm != nullptr && ctx->nranks > 1;
+    const bool use_p2p = sharded && ctx->p2p_ok && ctx->opt_p2p && g.n6 <= ctx->opt_p2p_max_n &&
+                         size_t(g.n6 + 1) * ws.ldA <= ctx->p2p_slab_floats;
+    if (use_p2p) {
+      // the rank's share goes into its exchange slab; ONE kernel signals, waits and sums all ranks' lower triangles
+      ++ctx->p2p_epoch;
+      const int parity = int(ctx->p2p_epoch & 1u);
+      Workspace wsx = ws;
+      wsx.A = ctx->p2p_buf + size_t(parity) * ctx->p2p_slab_floats;
+      CK(launch_assemble(g, in, wsx, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
+      mark();
+      CK(launch_p2p_allreduce(ctx->p2p_peers, ctx->nranks, ctx->rank, ctx->p2p_slab_floats, 2 * ctx->p2p_slab_floats,
+                              parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, st), "all-reduce (peer memory)");
+    } else {
     CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
     mark();
-    if (ctx->comm != nullptr && ctx->nranks > 1) {
+    }
+    if (sharded && !use_p2p) {
       const size_t cnt = size_t(g.n6 + 1) * ws.ldA;
       int r = g_nccl.AllReduce(ws.A, ws.A, cnt, /*ncclFloat32*/ 7, /*ncclSum*/ 0, ctx->comm, st);
       if (r != 0) {
@@ -597,6 +620,8 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "wide_tensor_cores") { ctx->opt_wide_tc = int(value); ctx->plan_valid = false; }
   else if (n == "small_system") ctx->opt_small = value != 0;
   else if (n == "refine") ctx->opt_refine = int(value);
+  else if (n == "p2p_allreduce") ctx->opt_p2p = value != 0;
+  else if (n == "p2p_max_n") ctx->opt_p2p_max_n = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
@@ -982,9 +1007,53 @@ int dba_comm_init(dba_ctx* ctx, int nranks, int rank, const void* id128) {
   return 0;
 }
 
+int dba_comm_p2p_export(dba_ctx* ctx, void* handle64_out, int64_t slab_bytes) {
+  if (!ctx || !handle64_out || slab_bytes <= 0) return -1;
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  if (ctx->p2p_buf) { cudaFree(ctx->p2p_buf); ctx->p2p_buf = nullptr; ctx->p2p_ok = false; }
+  const size_t slab_floats = (size_t(slab_bytes) / 4 + 3) & ~size_t(3);
+  void* p = nullptr;
+  CK(cudaMalloc(&p, (2 * slab_floats + 64) * sizeof(float)), "p2p buffer");
+  CK(cudaMemset(p, 0, (2 * slab_floats + 64) * sizeof(float)), "p2p buffer");
+  CK(cudaDeviceSynchronize(), "p2p buffer");
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) { cudaFree(p); return fail_cuda(ctx, e, "cudaIpcGetMemHandle"); }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  std::memcpy(handle64_out, &h, 64);
+  ctx->p2p_buf = static_cast<float*>(p);
+  ctx->p2p_slab_floats = slab_floats;
+  ctx->p2p_epoch = 0;
+  return 0;
+}
+
+int dba_comm_p2p_import(dba_ctx* ctx, const void* handles, int nranks) {
+  if (!ctx || !handles) return -1;
+  if (nranks != ctx->nranks || nranks > 8 || !ctx->p2p_buf) return fail_arg(ctx, "p2p import: call dba_comm_init and dba_comm_p2p_export first (<= 8 ranks)");
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  for (int r = 0; r < nranks; ++r) {
+    if (r == ctx->rank) { ctx->p2p_peers.base[r] = ctx->p2p_buf; continue; }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, static_cast<const char*>(handles) + 64 * r, 64);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { ctx->p2p_ok = false; return fail_cuda(ctx, e, "cudaIpcOpenMemHandle"); }
+    ctx->p2p_peers.base[r] = static_cast<float*>(p);
+  }
+  ctx->p2p_ok = true;
+  return 0;
+}
+
 int dba_comm_destroy(dba_ctx* ctx) {
   if (!ctx) return -1;
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  if (ctx->p2p_ok) {
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < ctx->nranks; ++r)
+      if (r != ctx->rank && ctx->p2p_peers.base[r]) cudaIpcCloseMemHandle(ctx->p2p_peers.base[r]);
+    ctx->p2p_ok = false;
+  }
   ctx->comm = nullptr; ctx->nranks = 1; ctx->rank = 0;
   return 0;
 }

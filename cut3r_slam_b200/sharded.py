@@ -56,7 +56,7 @@ class ShardedBA:
         self.ctx = droid_backends._Ctx(idx)
         self.rank, self.nranks = 0, 1
 
-    def init_comm(self):
+    def init_comm(self, p2p=True, p2p_slab_bytes=16 << 20):
         import torch.distributed as dist
         self.rank, self.nranks = dist.get_rank(), dist.get_world_size()
         if self.nranks == 1:
@@ -71,6 +71,23 @@ class ShardedBA:
         idbuf.raw = obj[0]
         with torch.cuda.device(self.device):
             self.ctx.check(self.ctx.lib.dba_comm_init(self.ctx.handle, self.nranks, self.rank, idbuf))
+            # peer-memory all-reduce for the small / medium systems (csrc/dba_p2p.cu); NCCL stays the path for the
+            # large ones and the fallback when the GPUs cannot map each other's memory
+            self.p2p = False
+            if p2p and self.nranks <= 8:
+                h = (C.c_char * 64)()
+                ok = self.ctx.lib.dba_comm_p2p_export(self.ctx.handle, h, int(p2p_slab_bytes)) == 0
+                handles = [None] * self.nranks
+                dist.all_gather_object(handles, bytes(h.raw) if ok else None)
+                if all(x is not None for x in handles):
+                    allh = (C.c_char * (64 * self.nranks))()
+                    allh.raw = b"".join(handles)
+                    self.p2p = self.ctx.lib.dba_comm_p2p_import(self.ctx.handle, allh, self.nranks) == 0
+                flag = torch.tensor([int(self.p2p)], device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)       # all ranks or none
+                self.p2p = bool(flag.item())
+                if not self.p2p:
+                    self.ctx.set_option("p2p_allreduce", 0)
 
     def close(self):
         self.ctx.lib.dba_comm_destroy(self.ctx.handle)

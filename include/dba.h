@@ -35,7 +35,10 @@ const char* dba_version(void);
  * system of the last iteration for dba_debug_read; "ppl" n -- pixels per lane override (0 = auto);
  * "profile" 0/1 -- bracket every stage with CUDA events on `stream` and accumulate per-stage times
  * (setting it resets the accumulators; the call then waits for its last event before returning);
- * "tensor_cores" 0/1 -- Schur products on tcgen05 (default 1); "wide_tensor_cores" 0/1/2 -- keyframes with
+ * "tensor_cores" 0/1 -- Schur products on tcgen05 (default 1); "linearize_v2" 0/1 -- the one-warp-per-edge kernel for
+ * out-degree <= 20 (default 1); "refine" 0/1/2 -- iterative refinement of the pose solve: off / last iteration of a call /
+ * every iteration (default 1); "cholesky_tc" n -- 128-column-panel factorisation with tcgen05 trailing update from system
+ * size n on (default 0 = off); "p2p_allreduce" 0/1, "p2p_max_n"; "stream_inputs" -1/0/1; "wide_tensor_cores" 0/1/2 -- keyframes with
  * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
 
@@ -176,6 +179,12 @@ int dba_cvx_upsample(dba_ctx* ctx, const float* data, const float* mask, int64_t
 int dba_nccl_unique_id(void* out128);                                   /* rank 0, then broadcast */
 int dba_comm_init(dba_ctx* ctx, int nranks, int rank, const void* id128);
 int dba_comm_destroy(dba_ctx* ctx);
+/* Optional, after dba_comm_init: replace the per-iteration ncclAllReduce by ONE kernel over NVLink peer memory for
+ * reduced systems up to option "p2p_max_n" (default 1536; larger ones stay on NCCL).  Every rank exports a buffer
+ * (two slabs of slab_bytes + flags; 64-byte cudaIpcMemHandle_t out), the handles are exchanged by the caller
+ * (rank order) and imported.  One process per GPU, all GPUs of one box with peer access. */
+int dba_comm_p2p_export(dba_ctx* ctx, void* handle64_out, int64_t slab_bytes);
+int dba_comm_p2p_import(dba_ctx* ctx, const void* handles /* [nranks][64] */, int nranks);
 
 /* ---- test / profiling hooks */
 /* name: "system" -> [(n6+1)*ld] floats of the last assembled reduced system (needs keep_system=1),
