@@ -133,6 +133,7 @@ struct dba_ctx {
   bool opt_p2p = true;
   int opt_p2p_max_n = 1536;          // larger systems are bandwidth-bound: NCCL's reduce-scatter + all-gather moves less
   uint32_t p2p_epoch = 0;
+  int opt_p2p_debug = 0;             // timing experiments only: 1 skip the flag wait, 2 skip the sums
   int64_t last_launches = 0;
   size_t smem_cap = 0;
 };
@@ -474,7 +475,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       CK(launch_assemble(g, in, wsx, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
       mark();
       CK(launch_p2p_allreduce(ctx->p2p_peers, ctx->nranks, ctx->rank, ctx->p2p_slab_floats, 2 * ctx->p2p_slab_floats,
-                              parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, st), "all-reduce (peer memory)");
+                              parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, ctx->opt_p2p_debug, st), "all-reduce (peer memory)");
     } else {
     CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
     mark();
@@ -622,6 +623,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "refine") ctx->opt_refine = int(value);
   else if (n == "p2p_allreduce") ctx->opt_p2p = value != 0;
   else if (n == "p2p_max_n") ctx->opt_p2p_max_n = int(value);
+  else if (n == "p2p_debug") ctx->opt_p2p_debug = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }

@@ -111,7 +111,7 @@ cudaError_t launch_depth_filter(const float* poses, const float* disps, const fl
 // sharded global BA: one-shot all-reduce of the reduced system over NVLink peer memory (dba_p2p.cu)
 struct P2PPeers { float* base[8]; };     // every rank's exchange buffer as mapped in THIS process (own rank: local)
 cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats,
-                                 int parity, uint32_t epoch, int ld, int n, float* out, int* err, cudaStream_t st);
+                                 int parity, uint32_t epoch, int ld, int n, float* out, int* err, int debug, cudaStream_t st);
 
 // JDSA path (dba_jdsa.cu)
 cudaError_t launch_proj_trans(const float* poses, const float* disps, const float* intr, const float* targets,

@@ -29,7 +29,7 @@ __device__ __forceinline__ float4 ld_peer(const float4* p) {     // bypass L1: t
 
 __global__ void __launch_bounds__(256)
 k_p2p_allreduce(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats, int parity,
-                uint32_t epoch, int ld, int n, float* __restrict__ out, int* __restrict__ err) {
+                uint32_t epoch, int ld, int n, float* __restrict__ out, int* __restrict__ err, int debug) {
   __shared__ int s_bad;
   const int tid = threadIdx.x, lane = tid & 31;
   if (tid == 0) s_bad = 0;
@@ -38,27 +38,41 @@ k_p2p_allreduce(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t
     st_release_sys(reinterpret_cast<uint32_t*>(peers.base[tid] + flags_off_floats) + rank, epoch);
   }
   __syncthreads();
-  if (tid < nranks) {                                // every CTA waits for all ranks' flags in MY buffer
+  if (tid < nranks && !(debug & 1)) {                // every CTA waits for all ranks' flags in MY buffer
     const uint32_t* f = reinterpret_cast<const uint32_t*>(peers.base[rank] + flags_off_floats) + tid;
     const long long t0 = clock64();
-    while (int32_t(ld_acquire_sys(f) - epoch) < 0) {
+    while (int32_t(*reinterpret_cast<const volatile uint32_t*>(f) - epoch) < 0) {    // polite polling: ~100 CTAs watch the line
+      __nanosleep(200);
       if (clock64() - t0 > 6000000000LL) { s_bad = 1; break; }       // ~3 s: a peer died; do not hang the GPU
     }
+    (void)ld_acquire_sys(f);                                         // order the slab reads after the flag
   }
   __syncthreads();
   if (s_bad && tid == 0) *err = 1;
   const int gw = blockIdx.x * 8 + (tid >> 5), nw = gridDim.x * 8;
   const size_t soff = size_t(parity) * slab_floats;
+  if (debug & 2) return;
   for (int i = n - gw; i >= 0; i -= nw) {            // long rows first; row n = rhs (n columns), row i < n: i + 1 columns
     const int ncol = (i < n) ? i + 1 : n;
     const size_t roff = soff + size_t(i) * ld;
-    for (int c4 = lane * 4; c4 < ncol; c4 += 128) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r = 0; r < nranks; ++r) {
-        const float4 v = ld_peer(reinterpret_cast<const float4*>(peers.base[r] + roff + c4));
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-      }
-      *reinterpret_cast<float4*>(out + size_t(i) * ld + c4) = acc;
+    for (int c4 = lane * 4; c4 < ncol; c4 += 256) {  // two chunks per pass, all ranks' loads in flight before the adds
+      const bool two = c4 + 128 < ncol;
+      float4 v0[8], v1[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < nranks) {
+          v0[r] = ld_peer(reinterpret_cast<const float4*>(peers.base[r] + roff + c4));
+          if (two) v1[r] = ld_peer(reinterpret_cast<const float4*>(peers.base[r] + roff + c4 + 128));
+        }
+      float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < nranks) {
+          a0.x += v0[r].x; a0.y += v0[r].y; a0.z += v0[r].z; a0.w += v0[r].w;
+          if (two) { a1.x += v1[r].x; a1.y += v1[r].y; a1.z += v1[r].z; a1.w += v1[r].w; }
+        }
+      *reinterpret_cast<float4*>(out + size_t(i) * ld + c4) = a0;
+      if (two) *reinterpret_cast<float4*>(out + size_t(i) * ld + c4 + 128) = a1;
     }
   }
 }
@@ -66,10 +80,10 @@ k_p2p_allreduce(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t
 }  // namespace
 
 cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats,
-                                 int parity, uint32_t epoch, int ld, int n, float* out, int* err, cudaStream_t st) {
+                                 int parity, uint32_t epoch, int ld, int n, float* out, int* err, int debug, cudaStream_t st) {
   int grid = (n + 1 + 7) / 8;
   if (grid > 296) grid = 296;
-  k_p2p_allreduce<<<grid, 256, 0, st>>>(peers, nranks, rank, slab_floats, flags_off_floats, parity, epoch, ld, n, out, err);
+  k_p2p_allreduce<<<grid, 256, 0, st>>>(peers, nranks, rank, slab_floats, flags_off_floats, parity, epoch, ld, n, out, err, debug);
   g_launch_count++;
   return cudaGetLastError();
 }
