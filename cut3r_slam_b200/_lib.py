@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdba.so")
+LIB_PATH = os.environ.get("DBA_LIB_PATH") or os.path.join(HERE, "libdba.so")     # override: developer builds (tracing)
 
 _lib = None
 

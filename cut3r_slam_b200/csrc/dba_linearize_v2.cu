@@ -18,6 +18,15 @@
 #include "dba_linearize.cuh"
 #include "dba_umma.cuh"
 
+// -DDBA_V2_TRACE: thread 0 (an owner, reducer and tail thread) and thread 64 (a flush warp) of CTA 0 print the clock
+// cycles they spent in every phase of the tile loop (developer experiment, profiles/r2_linearize_v2.md)
+#ifdef DBA_V2_TRACE
+#include <cstdio>
+#define TR(i) do { if (blockIdx.x == 0 && (tid == 0 || tid == 64)) { const long long t_ = clock64(); tr[i] += t_ - tlast; tlast = t_; } } while (0)
+#else
+#define TR(i) do { } while (0)
+#endif
+
 namespace dba {
 
 namespace {
@@ -166,8 +175,13 @@ k_linearize_v2(const LinParams P) {
     }
   };
 
+#ifdef DBA_V2_TRACE
+  long long tr[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  long long tlast = clock64(), trw = 0;
+#endif
 #pragma unroll 1
   for (int tile = tile_lo; tile < tile_hi; ++tile) {
+    TR(9);
     const int p0 = tile * T;
     const float* px = spx + (tile & 1) * 3 * T;
     float eta_n = 0.f, d_n = 0.f;                           // warps 0-1: eta and disparity of pixel (tile + 1, pl2)
@@ -236,13 +250,18 @@ k_linearize_v2(const LinParams P) {
       for (int i = 0; i < 8; ++i) cur[i] = 0.f;
       if (tile + 1 < tile_hi) load_inputs<STREAM>(tg, wg, HW, p0 + T, lane, cur);
     }
+    TR(0);
     __syncthreads();
+    TR(1);
     // ---------------- phase 2 (warps 0-1, one pixel each): the edges' partials summed in a fixed order; the other
     // warps meanwhile add the PREVIOUS tile's tensor-core products into the shared-memory accumulator ------------
     if (tile > tile_lo) {   // MMAs of the previous tile done: its accumulator readable, operand tiles reusable
       mbar_wait(&mbar[(tile - tile_lo - 1) & 1], uint32_t((tile - tile_lo - 1) >> 1) & 1u);
       tc_fence_after_sync();
     }
+#ifdef DBA_V2_TRACE
+    if (blockIdx.x == 0 && (tid == 0 || tid == 64)) { const long long t_ = clock64(); trw += t_ - tlast; tlast = t_; }
+#endif
     if (warp < 8) {         // four threads per pixel sum the edges' partials (fixed order), lane 0 of the four stores
       const int plr = tid >> 2, part = tid & 3;
       float sum[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
@@ -260,7 +279,9 @@ k_linearize_v2(const LinParams P) {
         for (int i = 0; i < 5; ++i) ssum[i * T + plr] = sum[i];
       }
     }
+    TR(2);
     __syncthreads();
+    TR(3);
     if (warp < 2) {         // one thread per pixel: Q, w, the source-pose rows
       float sum[5];
 #pragma unroll
@@ -304,7 +325,9 @@ k_linearize_v2(const LinParams P) {
       flush(((tile - tile_lo) & 1) ^ 1);
       tc_fence_before_sync();
     }
+    TR(4);
     __syncthreads();
+    TR(5);
     // ---------------- phase 3: operands for the tensor core ----------------------------------------------------
     {
       // half a warp per operand row, lane = 4 consecutive pixels = one 16-byte chunk of the swizzled K-major tile:
@@ -330,7 +353,9 @@ k_linearize_v2(const LinParams P) {
       }
     }
     fence_proxy_async_smem();
+    TR(6);
     __syncthreads();
+    TR(7);
     const int buf = (tile - tile_lo) & 1;
     if (tid == NT - 32) {                                   // the last warp owns an edge only when deg == NW
       tc_fence_after_sync();
@@ -356,7 +381,13 @@ k_linearize_v2(const LinParams P) {
         }
       mma_commit(&mbar[buf]);
     }
+    TR(8);
   }
+#ifdef DBA_V2_TRACE
+  if (blockIdx.x == 0 && (tid == 0 || tid == 64))
+    printf("v2 trace tid %d deg %d tiles %d: P1 %lld syncA %lld reduce %lld syncA2 %lld tail/flush %lld syncB %lld convert %lld syncC %lld mma %lld looptop %lld mbarwait %lld\n",
+           tid, deg, tile_hi - tile_lo, tr[0], tr[1], tr[2], tr[3], tr[4], tr[5], tr[6], tr[7], tr[8], tr[9], trw);
+#endif
   if (tile_lo < tile_hi) {
     const int last = tile_hi - tile_lo - 1;
     mbar_wait(&mbar[last & 1], uint32_t(last >> 1) & 1u);
