@@ -42,6 +42,9 @@ SIGNATURES = {
                                C.c_void_p]),
     "dba_jdsa": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
                            C.c_int, C.c_int, C.c_int, C.c_int64, C.c_float, C.c_float, C.c_float, c_f, C.c_void_p]),
+    "dba_pgba": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, c_i, c_i, c_f, c_f, C.c_int64, C.c_int64,
+                           C.c_int64, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float,
+                           c_f, c_f, C.c_void_p]),
     "dba_depth_cov": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int,
                                 C.c_int, C.c_int64, C.c_int, C.c_int, C.c_float, C.c_float, c_f, C.c_void_p]),
     "dba_rel_pose_cov": (C.c_int, [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_i, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int,

@@ -120,6 +120,10 @@ struct dba_ctx {
   DevBuf d_jd;                 // proj_trans outputs inside dba_jdsa
   DevBuf d_cov;                // L^-1 and S^-1 of dba_depth_cov
   DevBuf d_slot;               // dba_damping_gather: frame -> eta row
+  // dba_pgba (Sim3): its own plan (S = 1) and workspace
+  Plan pg_plan;
+  DevBuf pg_i32, pg_items, pg_H, pg_v, pg_Ep, pg_CW, pg_Q, pg_W, pg_Eis, pg_S, pg_vE, pg_Hsp, pg_vsp, pg_A, pg_Lm, pg_Ldiag,
+      pg_dx, pg_dz, pg_fail, pg_keep;
   int pt_M = 0, pt_N = 0;
   bool pt_contig = true;       // unique(ii) is a contiguous range of frames
   // NCCL
@@ -595,7 +599,9 @@ void dba_destroy(dba_ctx* c) {
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
-                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot};
+                    &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
+                    &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
+                    &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   if (c->side) cudaStreamDestroy(c->side);
@@ -681,6 +687,95 @@ int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, co
            int motion_only, float* dx_out, float* dz_out, void* stream) {
   return dba_ba_cached(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, E, N, ht, wd, M, t0,
                        t1, iterations, lm, ep, motion_only, dx_out, dz_out, stream, 0, nullptr, nullptr);
+}
+
+int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* targets, const float* weights,
+             const float* eta, const int64_t* ii, const int64_t* jj, const int64_t* rel_ii, const int64_t* rel_jj,
+             const float* rel_poses, const float* rel_infos, int64_t E, int64_t R, int64_t N, int ht, int wd, int64_t M,
+             int t0, int t1, int iterations, float lm, float ep, float pw, float* dx_out, float* dz_out, void* stream) {
+  int rc = check_common(ctx, poses, disps, intrinsics, targets, weights, eta, ii, jj, E, N, ht, wd, M, iterations, 0);
+  if (rc) return rc;
+  if (E <= 0) return fail_arg(ctx, "pgba needs reprojection edges");
+  if (R < 0 || (R > 0 && (!rel_ii || !rel_jj || !rel_poses || !rel_infos))) return fail_arg(ctx, "relative-pose factor arrays");
+  if (t0 < 0 || t1 <= t0 || t1 > N) return fail_arg(ctx, "need 0 <= t0 < t1 <= N");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+  rc = fetch_edge_lists(ctx, ii, jj, E, st);
+  if (rc) return rc;
+  const int64_t* ih = ctx->h_idx; const int64_t* jh = ctx->h_idx + E;
+  for (int64_t e = 0; e < E; ++e)
+    if (jh[e] < 0 || jh[e] >= t1 || ih[e] >= t1) return fail_arg(ctx, "edge index outside [0, t1)");
+  Plan& P = ctx->pg_plan;
+  const bool same = P.E == E && P.N == N && P.t0 == t0 && P.t1 == t1 && int64_t(P.key_ii.size()) == E &&
+                    std::memcmp(P.key_ii.data(), ih, E * sizeof(int64_t)) == 0 &&
+                    std::memcmp(P.key_jj.data(), jh, E * sizeof(int64_t)) == 0 && ctx->pg_i32.p != nullptr;
+  const size_t HW = size_t(ht) * wd, f = sizeof(float);
+  auto r4 = [](size_t n) { return (n + 3) & ~size_t(3); };
+  if (!same) {
+    P = Plan();
+    if (!build_plan(P, ih, jh, E, int(N), t0, t1, false, M, 1)) return fail_arg(ctx, P.error);
+    std::vector<int32_t> pack;
+    auto put = [&](const std::vector<int32_t>& v) { pack.insert(pack.end(), v.begin(), v.end()); while (pack.size() % 4) pack.push_back(0); };
+    put(P.kx); put(P.koff); put(P.cedge); put(P.ci); put(P.cj); put(P.pairbase); put(P.blkbase); put(P.sblk_off); put(P.rhs_off);
+    CK(ctx->pg_i32.ensure(pack.size() * 4 + 16), "pgba plan");
+    CK(cudaMemcpyAsync(ctx->pg_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "pgba plan");
+    std::vector<Item> items(P.sblk_items);
+    items.insert(items.end(), P.rhs_items.begin(), P.rhs_items.end());
+    CK(ctx->pg_items.ensure(items.size() * sizeof(Item) + 16), "pgba plan");
+    if (!items.empty()) CK(cudaMemcpyAsync(ctx->pg_items.p, items.data(), items.size() * sizeof(Item), cudaMemcpyHostToDevice, st), "pgba plan");
+    CK(cudaStreamSynchronize(st), "pgba plan");
+  } else if (M != P.M) return fail_arg(ctx, "eta rows != |unique(ii)|");
+  const int Pp = P.Pp, n7 = 7 * Pp, ld = (n7 + 1 + 3) & ~3;
+  CK(ctx->pg_H.ensure(size_t(E) * 4 * 49 * f), "pgba workspace");  CK(ctx->pg_v.ensure(size_t(E) * 14 * f), "pgba workspace");
+  CK(ctx->pg_Ep.ensure(size_t(E) * 14 * HW * f), "pgba workspace"); CK(ctx->pg_CW.ensure(size_t(E) * 2 * HW * f), "pgba workspace");
+  CK(ctx->pg_Q.ensure(size_t(P.M) * HW * f), "pgba workspace");     CK(ctx->pg_W.ensure(size_t(P.M) * HW * f), "pgba workspace");
+  CK(ctx->pg_Eis.ensure(size_t(P.M) * 7 * HW * f), "pgba workspace"); CK(ctx->pg_dz.ensure(size_t(P.M) * HW * f), "pgba workspace");
+  CK(ctx->pg_S.ensure(size_t(P.pairbase[P.M]) * 49 * f + 16), "pgba workspace");
+  CK(ctx->pg_vE.ensure(size_t(P.blkbase[P.M]) * 7 * f + 16), "pgba workspace");
+  CK(ctx->pg_Hsp.ensure(size_t(R) * 4 * 49 * f + 16), "pgba workspace"); CK(ctx->pg_vsp.ensure(size_t(R) * 14 * f + 16), "pgba workspace");
+  CK(ctx->pg_A.ensure(size_t(n7 + 1) * ld * f, true), "pgba workspace"); CK(ctx->pg_Lm.ensure(size_t(n7 + 1) * ld * f), "pgba workspace");
+  CK(ctx->pg_keep.ensure(size_t(n7 + 1) * ld * f), "pgba workspace");
+  CK(ctx->pg_Ldiag.ensure(cholesky_ldiag_floats(n7) * f + 16), "pgba workspace");
+  CK(ctx->pg_dx.ensure(size_t(n7) * f + 16), "pgba workspace"); CK(ctx->pg_fail.ensure(16, true), "pgba workspace");
+  const int32_t* b = ctx->pg_i32.as<int32_t>();
+  PgbaArgs a{};
+  a.poses = poses; a.disps = disps; a.intr = intrinsics; a.targets = targets; a.weights = weights; a.eta = eta;
+  a.kx = b; b += r4(P.kx.size()); a.koff = b; b += r4(P.koff.size()); a.cedge = b; b += r4(P.cedge.size());
+  a.ci = b; b += r4(P.ci.size()); a.cj = b; b += r4(P.cj.size()); a.pairbase = b; b += r4(P.pairbase.size());
+  a.blkbase = b; b += r4(P.blkbase.size()); a.sblk_off = b; b += r4(P.sblk_off.size()); a.rhs_off = b;
+  a.sblk_items = ctx->pg_items.as<Item>(); a.rhs_items = a.sblk_items + P.sblk_items.size();
+  a.rel_ii = rel_ii; a.rel_jj = rel_jj; a.rel_poses = rel_poses; a.rel_infos = rel_infos; a.pw = pw; a.lm = lm; a.ep = ep;
+  a.E = int(E); a.N = int(N); a.M = P.M; a.R = int(R); a.HW = int(HW); a.wd = wd; a.t0 = t0; a.Pp = Pp; a.nSblk = P.nSblk;
+  a.npairs_max = P.npairs_max; a.ldA = ld;
+  a.Hblk = ctx->pg_H.as<float>(); a.vblk = ctx->pg_v.as<float>(); a.Ep = ctx->pg_Ep.as<float>(); a.CW = ctx->pg_CW.as<float>();
+  a.Q = ctx->pg_Q.as<float>(); a.Wv = ctx->pg_W.as<float>(); a.Eis = ctx->pg_Eis.as<float>(); a.Spart = ctx->pg_S.as<float>();
+  a.vEpart = ctx->pg_vE.as<float>(); a.Hsp = ctx->pg_Hsp.as<float>(); a.vsp = ctx->pg_vsp.as<float>(); a.A = ctx->pg_A.as<float>();
+  a.dx = ctx->pg_dx.as<float>(); a.dz = ctx->pg_dz.as<float>();
+  Workspace ws{};
+  ws.A = a.A; ws.ldA = ld; ws.Lm = ctx->pg_Lm.as<float>(); ws.Ldiag = ctx->pg_Ldiag.as<float>(); ws.dx = a.dx;
+  ws.fail = ctx->pg_fail.as<int>();
+  const int coop = cholesky_coop_max_ctas(n7);
+  g_launch_count = 0;
+  for (int it = 0; it < iterations; ++it) {
+    CK(launch_pgba_linearize(a, st), "pgba linearize");
+    if (n7 <= cholesky_small_max_n()) {
+      CK(launch_cholesky_small(ws, n7, st), "cholesky (single CTA)");
+    } else if (coop > 0) {
+      const bool refine = ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it == iterations - 1);
+      if (refine) CK(cudaMemcpyAsync(ctx->pg_keep.p, a.A, size_t(n7 + 1) * ld * f, cudaMemcpyDeviceToDevice, st), "pgba keep");
+      CK(launch_cholesky_coop(ws, n7, coop, st, !refine), "cholesky (cooperative)");
+      if (refine) CK(launch_refine(ws, ctx->pg_keep.as<float>(), n7, st), "refinement");
+    } else {
+      return fail_arg(ctx, "pgba: reduced system too large for the cooperative factorisation");
+    }
+    CK(launch_pgba_update(a, (it == iterations - 1) ? dx_out : nullptr, st), "pgba update");
+  }
+  if (iterations > 0) {
+    CK(launch_pgba_guard(disps, int64_t(t1) * int64_t(HW), st), "guard");
+    if (dz_out) CK(cudaMemcpyAsync(dz_out, a.dz, size_t(P.M) * HW * f, cudaMemcpyDeviceToDevice, st), "dz_out");
+  }
+  ctx->last_launches = g_launch_count;
+  return 0;
 }
 
 int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* disps_sens,

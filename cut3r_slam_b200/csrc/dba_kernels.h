@@ -113,6 +113,23 @@ struct P2PPeers { float* base[8]; };     // every rank's exchange buffer as mapp
 cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats,
                                  int parity, uint32_t epoch, int ld, int n, float* out, int* err, int debug, cudaStream_t st);
 
+// pgba: Sim3 pose-graph BA (dba_pgba.cu); all device pointers, the plan arrays as uploaded for the 6-dof path
+struct PgbaArgs {
+  float* poses;              // [N,8] Sim3, in place
+  float* disps;              // [N,HW] in place
+  const float *intr, *targets, *weights, *eta;
+  const int32_t *kx, *koff, *cedge, *ci, *cj, *pairbase, *blkbase, *sblk_off, *rhs_off;
+  const Item *sblk_items, *rhs_items;
+  const int64_t *rel_ii, *rel_jj;      // [R] device
+  const float *rel_poses, *rel_infos;  // [R,7], [R,7,7]
+  float pw, lm, ep;
+  int E, N, M, R, HW, wd, t0, Pp, nSblk, npairs_max, ldA;
+  float *Hblk, *vblk, *Ep, *CW, *Q, *Wv, *Eis, *Spart, *vEpart, *Hsp, *vsp, *A, *dx, *dz;
+};
+cudaError_t launch_pgba_linearize(const PgbaArgs& a, cudaStream_t st);
+cudaError_t launch_pgba_update(const PgbaArgs& a, float* dx_out, cudaStream_t st);
+cudaError_t launch_pgba_guard(float* disps, int64_t n, cudaStream_t st);
+
 // JDSA path (dba_jdsa.cu)
 cudaError_t launch_proj_trans(const float* poses, const float* disps, const float* intr, const float* targets,
                               const float* weights, const int32_t* kx, const int32_t* koff, const int32_t* cedge,

@@ -171,6 +171,54 @@ def ba(*args, _ctx=None):
     return [dx, dz]
 
 
+def pgba(poses, disps, intrinsics, targets, weights, eta, ii, jj, rel_ii, rel_jj, rel_poses, rel_infos, t0, t1,
+         iterations, lm, ep, pw=1e-5, motion_only=False):
+    """droid_backends.pgba -- Sim3 pose-graph bundle adjustment (19 arguments, like the absent export called at
+    depth_video.pyc cuda_pgba@307-309; its exact argument order is not recoverable, this one is documented in
+    include/dba.h).  poses [N,8] Sim3 ([t, q, s]: `video.poses_sim3`) and disps are updated in place;
+    rel_ii / rel_jj [R] int64, rel_poses [R,7], rel_infos [R,7,7] are the relative-pose factors of PGOBuffer
+    (hislam2/pgo_buffer.py:39-62; pass empty tensors for none).  Returns [dx [t1-t0,7], dz [M,ht,wd]]."""
+    if motion_only:
+        raise RuntimeError("pgba: motion_only is not supported")
+    _check(poses, "poses", torch.float32, 2)
+    if poses.shape[1] != 8:
+        raise RuntimeError(f"poses must be [N,8] Sim3 data, got {tuple(poses.shape)}")
+    _check(disps, "disps", torch.float32, 3)
+    _check(intrinsics, "intrinsics", torch.float32, 1)
+    _check(targets, "targets", torch.float32, 4)
+    _check(weights, "weights", torch.float32, 4)
+    _check(eta, "eta", torch.float32, 3)
+    _check(ii, "ii", torch.int64, 1)
+    _check(jj, "jj", torch.int64, 1)
+    N, ht, wd = disps.shape
+    E, M = ii.numel(), eta.shape[0]
+    if poses.shape[0] != N or jj.numel() != E:
+        raise RuntimeError("poses / disps / ii / jj sizes disagree")
+    for t, nm in ((targets, "targets"), (weights, "weights")):
+        if tuple(t.shape) != (E, 2, ht, wd):
+            raise RuntimeError(f"{nm} must be [{E},2,{ht},{wd}], got {tuple(t.shape)}")
+    R = 0 if rel_ii is None else rel_ii.numel()
+    if R:
+        _check(rel_ii, "rel_ii", torch.int64, 1)
+        _check(rel_jj, "rel_jj", torch.int64, 1)
+        _check(rel_poses, "rel_poses", torch.float32, 2)
+        _check(rel_infos, "rel_infos", torch.float32, 3)
+        if rel_jj.numel() != R or tuple(rel_poses.shape) != (R, 7) or tuple(rel_infos.shape) != (R, 7, 7):
+            raise RuntimeError("relative-pose factors: rel_jj [R], rel_poses [R,7], rel_infos [R,7,7]")
+    t0, t1, iterations = int(t0), int(t1), int(iterations)
+    dx = torch.zeros((max(t1 - t0, 0), 7), dtype=torch.float32, device=poses.device)
+    dz = torch.zeros((M, ht, wd), dtype=torch.float32, device=poses.device)
+    ctx = context(poses.device)
+    with torch.cuda.device(poses.device):
+        stream = torch.cuda.current_stream(poses.device).cuda_stream
+        rc = ctx.lib.dba_pgba(ctx.handle, _ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(targets), _ptr(weights), _ptr(eta),
+                              _ptr(ii), _ptr(jj), _ptr(rel_ii if R else None), _ptr(rel_jj if R else None),
+                              _ptr(rel_poses if R else None), _ptr(rel_infos if R else None), E, R, N, ht, wd, M, t0, t1,
+                              iterations, float(lm), float(ep), float(pw), _ptr(dx), _ptr(dz), C.c_void_p(stream))
+    ctx.check(rc)
+    return [dx, dz]
+
+
 def depth_cov(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, lm, ep):
     """The depth covariance the reference's torch BA returns as its third output (hislam2/geom/ba.py:98-107,
     chol.py:74-76), at the given state and with the argument list of `ba` (no iterations / motion_only):

@@ -127,6 +127,20 @@ int dba_jdsa(dba_ctx* ctx, const float* poses, float* disps, const float* intrin
              const int64_t* jj, int64_t E, int64_t N, int ht, int wd, int hs, int ws, int64_t M, float alpha, float ep,
              float lm, float* dzcov_out, void* stream);
 
+/* ---- pgba: Sim3 pose-graph bundle adjustment.  Replaces droid_backends.pgba (19 arguments at
+ * depth_video.pyc cuda_pgba@307-309; CUDA source absent).  `iterations` steps of: the reference's BA (hislam2/geom/ba.py:
+ * 32-107) with Sim3 poses (7-dof; geom/projective_ops.py:32-38, thirdparty/lietorch/lietorch/include/sim3.h) plus the
+ * relative-pose factors of hislam2/pgo_buffer.py:39-62 (residual log(Gij G_i G_j^-1), numeric Jacobians in fp64, blocks
+ * scaled by pw and the 7x7 information matrices) added to H, v before the LM damping (that composition is bytecode-only
+ * in the reference: parity unpinned; the two parts are pinned, tests/golden/pgba.npz).
+ *   poses [N,8] in/out [tx,ty,tz,qx,qy,qz,qw,s]; disps, targets, weights, eta, ii, jj as dba_ba (indices < t1);
+ *   rel_ii, rel_jj [R] int64 device, rel_poses [R,7] (SE3, scale 1), rel_infos [R,7,7]; R may be 0;
+ *   dx_out [t1-t0,7] or NULL, dz_out [M,ht,wd] or NULL.  Synchronises `stream` once (plan on the host). */
+int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* targets, const float* weights,
+             const float* eta, const int64_t* ii, const int64_t* jj, const int64_t* rel_ii, const int64_t* rel_jj,
+             const float* rel_poses, const float* rel_infos, int64_t E, int64_t R, int64_t N, int ht, int wd, int64_t M,
+             int t0, int t1, int iterations, float lm, float ep, float pw, float* dx_out, float* dz_out, void* stream);
+
 /* ---- depth covariance of the Schur solve: the third output of BA (hislam2/geom/ba.py:98-107, chol.py:74-76;
  * SURVEY.md 8f rank 4).  Linearises at the GIVEN state exactly as one `ba` iteration would (same arguments, same
  * damping lm / ep), factors the reduced pose system and writes dzcov [M,ht,wd] = diag(E^T S^-1 E) Q^2 + Q, rows in
