@@ -130,6 +130,9 @@ cudaError_t launch_pgba_linearize(const PgbaArgs& a, cudaStream_t st);
 cudaError_t launch_pgba_update(const PgbaArgs& a, float* dx_out, cudaStream_t st);
 cudaError_t launch_pgba_guard(float* disps, int64_t n, cudaStream_t st);
 
+size_t tri_pack_floats(int n);
+cudaError_t launch_tri_pack(float* A, float* buf, int ld, int n, bool pack, cudaStream_t st);
+
 // JDSA path (dba_jdsa.cu)
 cudaError_t launch_proj_trans(const float* poses, const float* disps, const float* intr, const float* targets,
                               const float* weights, const int32_t* kx, const int32_t* koff, const int32_t* cedge,

@@ -77,6 +77,23 @@ k_p2p_allreduce(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t
   }
 }
 
+// NCCL path of the large systems: only the lower triangle + rhs row carry data, so they are packed into a contiguous
+// buffer (row i at i (i + 1) / 2, the rhs row behind the triangle), all-reduced and unpacked: half the bytes on NVLink.
+template <bool PACK>
+__global__ void __launch_bounds__(256)
+k_tri_pack(float* __restrict__ A, float* __restrict__ buf, int ld, int n) {
+  const int lane = threadIdx.x & 31;
+  const int gw = blockIdx.x * 8 + (threadIdx.x >> 5), nw = gridDim.x * 8;
+  for (int i = gw; i <= n; i += nw) {
+    const int ncol = (i < n) ? i + 1 : n;
+    float* row = A + size_t(i) * ld;
+    float* dst = buf + (size_t(i) * (i + 1)) / 2;          // i = n: n (n + 1) / 2 = the rhs row's slot
+    for (int c = lane; c < ncol; c += 32) {
+      if (PACK) dst[c] = row[c]; else row[c] = dst[c];
+    }
+  }
+}
+
 }  // namespace
 
 cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats,
@@ -88,4 +105,16 @@ cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, si
   return cudaGetLastError();
 }
 
+}  // namespace dba
+
+namespace dba {
+size_t tri_pack_floats(int n) { return size_t(n) * (n + 1) / 2 + size_t(n); }
+cudaError_t launch_tri_pack(float* A, float* buf, int ld, int n, bool pack, cudaStream_t st) {
+  int grid = (n + 1 + 7) / 8;
+  if (grid > 592) grid = 592;
+  if (pack) k_tri_pack<true><<<grid, 256, 0, st>>>(A, buf, ld, n);
+  else k_tri_pack<false><<<grid, 256, 0, st>>>(A, buf, ld, n);
+  g_launch_count++;
+  return cudaGetLastError();
+}
 }  // namespace dba

@@ -106,13 +106,26 @@ class ShardedBA:
         return droid_backends.stage_times(_ctx=self.ctx)
 
     def gather_disps(self, disps, shards):
-        """Make every rank's disps complete again: each rank broadcasts the rows of its keyframes."""
+        """Make every rank's disps complete again: ONE all-gather of the ranks' keyframe rows (padded to the longest
+        shard) and one indexed copy; the index tensors are built once per shard layout."""
         import torch.distributed as dist
-        for r, sh in enumerate(shards):
-            rows = sh["keyframes"].to(disps.device)
-            if rows.numel() == 0:
-                continue
-            buf = disps[rows].contiguous()
-            dist.broadcast(buf, src=r)
-            disps[rows] = buf
+        if self.nranks == 1:
+            return disps
+        key = (id(shards), disps.device.index)
+        lay = getattr(self, "_gather_layout", None)
+        if lay is None or lay[0] != key:
+            lens = [int(sh["keyframes"].numel()) for sh in shards]
+            maxr = max(max(lens), 1)
+            rows = torch.cat([sh["keyframes"] for sh in shards]).to(disps.device)
+            src = torch.cat([r * maxr + torch.arange(n) for r, n in enumerate(lens)]).to(disps.device)
+            mine = shards[self.rank]["keyframes"].to(disps.device)
+            send = torch.zeros((maxr,) + tuple(disps.shape[1:]), dtype=disps.dtype, device=disps.device)
+            recv = torch.empty((self.nranks * maxr,) + tuple(disps.shape[1:]), dtype=disps.dtype, device=disps.device)
+            lay = (key, rows, src, mine, send, recv)
+            self._gather_layout = lay
+        _, rows, src, mine, send, recv = lay
+        if mine.numel():
+            send[:mine.numel()] = disps[mine]
+        dist.all_gather_into_tensor(recv, send)
+        disps[rows] = recv[src]
         return disps
