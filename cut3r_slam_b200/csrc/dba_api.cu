@@ -202,7 +202,17 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
       if (dg[f] > 0 && dg[f] <= linearize_tc_max_degree()) { ++n_tc_kf; if (dg[f] > degmax_tc) degmax_tc = dg[f]; }
     if (n_tc_kf > 0 && linearize_tc_smem_bytes(degmax_tc) > ctx->smem_cap) n_tc_kf = 0;
   }
-  const bool use_tc = n_tc_kf > 0;
+  bool use_tc = n_tc_kf > 0;
+  if (use_tc) {
+    // keyframes beyond the widest tcgen05 variant take the SIMT kernel, whose panel must fit at the tcgen05 tile
+    // width (ppl = 2: out-degree <~ 105); if it does not, the whole graph takes the SIMT kernel with a narrower tile
+    // (out-degree <~ 200) instead of being rejected
+    const int tc_cap = ctx->opt_wide_tc >= 2 ? linearize_tc_wide_max_degree(2)
+                     : ctx->opt_wide_tc >= 1 ? linearize_tc_wide_max_degree(1) : linearize_tc_max_degree();
+    if (degmax > tc_cap && linearize_smem_bytes(degmax, linearize_tc_ppl(), motion_only) > ctx->smem_cap) {
+      use_tc = false; n_tc_kf = 0; degmax_tc = 0;
+    }
+  }
   const bool use_v2 = use_tc && ctx->opt_v2 && linearize_v2_smem_bytes(degmax_tc) <= ctx->smem_cap;
   int ppl = use_tc ? linearize_tc_ppl()
                    : (ctx->opt_ppl > 0 ? ctx->opt_ppl : linearize_pick_ppl(degmax, degmax + 1, motion_only, HW, ctx->smem_cap));

@@ -346,3 +346,26 @@ def test_tensor_core_cholesky_agrees(P, E):
     assert float((b.poses - a.poses).abs().max()) < 1e-4
     ref_p, ref_d = od.oracle_ba(*p.ba_args(), dtype=torch.float64)
     assert rel_err(b.disps.cpu(), ref_d) < 1e-4
+
+
+def test_hub_keyframe_next_to_tensor_core_keyframes():
+    """One keyframe with 120 outgoing edges (beyond every tcgen05 variant and beyond the SIMT panel at the tcgen05 tile
+    width) in a graph whose other keyframes would take the tensor-core kernels: the plan falls back to the SIMT kernel
+    with a narrower tile for the whole graph instead of rejecting it (dba_api.cu)."""
+    db = _db()
+    p = make_problem(P=124, E=246, ht=8, wd=12, iters=1, t0=1, r=1, seed=77)          # radius-1 chain: 246 edges
+    hub = torch.arange(3, 123)
+    ii = torch.cat([p.ii, torch.full((120,), 1, dtype=torch.long)])
+    jj = torch.cat([p.jj, hub])
+    gen = torch.Generator().manual_seed(9)
+    tg = torch.cat([p.targets, p.targets[:120] + 0.1 * torch.randn(120, 2, 8, 12, generator=gen)])
+    wg = torch.cat([p.weights, torch.rand(120, 2, 8, 12, generator=gen)])
+    args = (p.poses, p.disps, p.intrinsics, None, tg.contiguous(), wg.contiguous(), p.eta, ii, jj, p.t0, p.t1, 1, p.lm,
+            p.ep, False)
+    ref_p, ref_d, infos = od.oracle_ba(*args, dtype=torch.float64, return_info=True)
+    _, _, infos32 = od.oracle_ba(*args, dtype=torch.float32, return_info=True)
+    g = [a.cuda() if isinstance(a, torch.Tensor) else a for a in args]
+    dx, dz = db.ba(*g)
+    gap = rel_err(infos32[0][0], infos[0][0])
+    assert rel_err(dx.cpu(), infos[0][0]) < MULT * gap + 1e-5, gap
+    assert rel_err(g[1].cpu(), ref_d) < 1e-4
