@@ -55,6 +55,8 @@ SIGNATURES = {
                                       c_f, c_f, c_f, C.c_void_p]),
     "dba_damping_gather": (C.c_int, [C.c_void_p, c_f, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int64, c_f,
                                      C.c_void_p]),
+    "dba_damping_gather_noalloc": (C.c_int, [C.c_void_p, c_f, c_i, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int64, c_f,
+                                             C.c_void_p]),
     "dba_cvx_upsample": (C.c_int, [C.c_void_p, c_f, c_f, C.c_int64, C.c_int, C.c_int, C.c_int, c_f, C.c_void_p]),
     "dba_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "dba_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),

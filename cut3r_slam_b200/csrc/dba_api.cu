@@ -578,6 +578,15 @@ int check_common(dba_ctx* ctx, const void* poses, const void* disps, const void*
 
 }  // namespace
 
+// accessors for entry points defined beside their kernels in another translation unit (dba_glue.cu:
+// dba_damping_gather_noalloc); dba_ctx itself is private to this file
+namespace dba {
+int ctx_device(dba_ctx* c) { return c->device; }
+int ctx_fail_arg(dba_ctx* c, const char* m) { return fail_arg(c, m); }
+int ctx_fail_cuda(dba_ctx* c, cudaError_t e, const char* where) { return fail_cuda(c, e, where); }
+void ctx_set_launches(dba_ctx* c, int64_t n) { c->last_launches = n; }
+}  // namespace dba
+
 extern "C" {
 
 const char* dba_version(void) { return "libdba 0.1 (sm_100a)"; }

@@ -7,6 +7,11 @@
 // Both are HBM-bound streaming kernels: every input element is read once with full 128-byte warp transactions,
 // every output written once (the upsampler transposes its 8x8 sub-pixel block through shared memory so that the
 // rows of the fine image leave as contiguous runs).
+#include "../../include/dba.h"
+
+#include <climits>
+#include <mutex>
+
 #include "dba_kernels.h"
 #include "dba_math.cuh"
 
@@ -285,3 +290,64 @@ cudaError_t launch_cvx_upsample(const float* data, const float* mask, int B, int
 }
 
 }  // namespace dba
+
+// ---- dba_damping_gather_noalloc: the damping gather for callers that must not allocate (code under CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same two kernels as dba_damping_gather; the frame -> row map (the only scratch of this op)
+// lives in a file-scope device array instead of the context's growable buffer.
+//
+// kNoAllocMaxFrames * 4 bytes = 48 000 bytes are held by every GPU that loads the library, until the process exits.
+// Every call on a device shares the array: k_source_slots rewrites entries [0, N) in full before k_damping_gather
+// reads them, so nothing has to start at zero and stale contents of an earlier call are never read -- but two calls
+// that overlap on the GPU (different streams, no ordering between them) race on it.
+namespace dba {
+namespace {
+constexpr int kNoAllocMaxFrames = 12000;          // = the frame limit of dba_damping_gather
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) int32_t g_noalloc_slot[kNoAllocMaxFrames];
+
+// In host code `g_noalloc_slot` is only a stand-in for the symbol, not a device address: the address is looked up
+// once per device, with that device current, and cached.
+int32_t* g_noalloc_slot_addr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+
+cudaError_t noalloc_slot_address(int device, int32_t** out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_slot_addr[device] == nullptr) {
+    int32_t* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_slot);
+    if (e != cudaSuccess) return e;
+    if (p == nullptr) return cudaErrorInvalidSymbol;
+    g_noalloc_slot_addr[device] = p;
+  }
+  *out = g_noalloc_slot_addr[device];
+  return cudaSuccess;
+}
+}  // namespace
+}  // namespace dba
+
+extern "C" int dba_damping_gather_noalloc(dba_ctx* ctx, const float* damping, const int64_t* ii, int64_t E, int64_t N,
+                                          int ht, int wd, int64_t M, float* eta_out, void* stream) {
+  using namespace dba;
+  if (!ctx) return -1;
+  if (E < 0 || N <= 0 || ht <= 0 || wd <= 0 || M < 0) return ctx_fail_arg(ctx, "negative or zero size");
+  if (N > kNoAllocMaxFrames)
+    return ctx_fail_arg(ctx, "dba_damping_gather_noalloc: frame buffer larger than the static scratch (12000 frames)");
+  if (E > INT32_MAX || int64_t(ht) * wd > INT32_MAX || M > INT32_MAX)
+    return ctx_fail_arg(ctx, "dba_damping_gather_noalloc: size beyond int32");
+  if (E == 0 || M == 0) return 0;
+  if (!damping || !ii || !eta_out) return ctx_fail_arg(ctx, "NULL argument");
+  const int device = ctx_device(ctx);
+  if (device < 0 || device >= kNoAllocMaxDevices) return ctx_fail_arg(ctx, "dba_damping_gather_noalloc: device index beyond 63");
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return ctx_fail_cuda(ctx, e, "cudaSetDevice");
+  int32_t* slot = nullptr;
+  e = noalloc_slot_address(device, &slot);
+  if (e != cudaSuccess) return ctx_fail_cuda(ctx, e, "cudaGetSymbolAddress(g_noalloc_slot)");
+  g_launch_count = 0;
+  e = launch_damping_gather(damping, ii, int(E), int(N), ht * wd, int(M), slot, eta_out,
+                            reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return ctx_fail_cuda(ctx, e, "damping_gather_noalloc");
+  ctx_set_launches(ctx, g_launch_count);
+  return 0;
+}

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 
+struct dba_ctx;
+
 namespace dba {
 
 struct Item;
@@ -160,5 +162,11 @@ size_t jdsa_dynamic_smem(int ht, int wd);
 cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const float* eta, const float* prior,
                         float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,
                         float ep, float lm, float* dzcov, float* dz_out, float* dso_out, cudaStream_t st);
+
+// dba_ctx accessors (dba_api.cu) for entry points that live beside their kernels
+int ctx_device(::dba_ctx* c);
+int ctx_fail_arg(::dba_ctx* c, const char* m);
+int ctx_fail_cuda(::dba_ctx* c, cudaError_t e, const char* where);
+void ctx_set_launches(::dba_ctx* c, int64_t n);
 
 }  // namespace dba

@@ -143,3 +143,23 @@ def damping_eta(damping, ii):
         ctx.check(ctx.lib.dba_damping_gather(ctx.handle, _ptr(damping), _ptr(ii), ii.numel(), N, ht, wd, M, _ptr(eta),
                                              C.c_void_p(stream)))
     return eta
+
+
+def damping_eta_noalloc(damping, ii, eta_out):
+    """damping_eta through dba_damping_gather_noalloc (include/dba.h): no allocation anywhere on the path -- the caller
+    passes the output eta_out [M,ht,wd] (M = |unique(ii)|, which the caller knows: it sized eta_out), the frame -> row
+    map lives in the library's static device array (N <= 12000 frames).  No counterpart in the reference.  Calls that
+    overlap on the GPU share that array and race: keep them on one stream."""
+    _check(damping, "damping", torch.float32, 3)
+    _check(ii, "ii", torch.int64, 1)
+    _check(eta_out, "eta_out", torch.float32, 3)
+    N, ht, wd = damping.shape
+    M = eta_out.shape[0]
+    if tuple(eta_out.shape[1:]) != (ht, wd) or eta_out.device != damping.device:
+        raise ValueError("eta_out must be [M,ht,wd] on damping's device")
+    ctx = context(damping.device)
+    with torch.cuda.device(damping.device):
+        stream = torch.cuda.current_stream(damping.device).cuda_stream
+        ctx.check(ctx.lib.dba_damping_gather_noalloc(ctx.handle, _ptr(damping), _ptr(ii), ii.numel(), N, ht, wd, M,
+                                                     _ptr(eta_out), C.c_void_p(stream)))
+    return eta_out

@@ -181,6 +181,17 @@ int dba_motion_features(dba_ctx* ctx, const float* poses, const float* disps, co
  *   caller knows it: it sizes eta); unique / rank are computed on the device, no host round trip. */
 int dba_damping_gather(dba_ctx* ctx, const float* damping, const int64_t* ii, int64_t E, int64_t N, int ht, int wd,
                        int64_t M, float* eta_out, void* stream);
+/* dba_damping_gather without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ *   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ *   that forbid it).  Same arguments, same kernels and bit-identical output to dba_damping_gather; the frame -> row
+ *   map, the only scratch of this op, lives in a file-scope `static __device__` array of 12000 int32 (48 000 bytes
+ *   held by every GPU that loads the library until the process exits) whose device address is looked up once per
+ *   device with cudaGetSymbolAddress.  Calls no cudaMalloc / cudaFree / allocating library routine.
+ *   N > 12000 is rejected (<0, message via dba_last_error).  All calls on one device share the array (entries [0, N)
+ *   are rewritten in full by every call, nothing needs clearing): calls that OVERLAP on the GPU -- different streams
+ *   without an ordering between them -- race; order them on one stream or with events. */
+int dba_damping_gather_noalloc(dba_ctx* ctx, const float* damping, const int64_t* ii, int64_t E, int64_t N, int ht,
+                               int wd, int64_t M, float* eta_out, void* stream);
 /* cvx_upsample(data, mask) -> up  [hislam2/modules/droid_net.py:21-38; upsample_disp :40-44 is dim = 1]:
  *   data [B,ht,wd,dim], mask [B,576,ht,wd] (= [B,9,8,8,ht,wd] logits), up [B,8ht,8wd,dim].  `mask` is read-only
  *   here (the reference writes -inf into the border entries of the caller's tensor as a side effect). */
