@@ -27,6 +27,14 @@
 #define TR(i) do { } while (0)
 #endif
 
+// -DDBA_V2_ABLATE=bits (developer timing experiment through tools/build_v2_variant.sh, results are WRONG): 1 no MMAs,
+// 2 only the hi x hi product, 4 no flush, 8 no operand conversion, 16 no reduce / tail, 32 no phase-1 arithmetic.
+// Reading the deltas: switching a consumer off also removes the producer code that feeds it (dead-code elimination),
+// so the deltas over-attribute; profiles/r2c_linearize_experiments.md.
+#ifndef DBA_V2_ABLATE
+#define DBA_V2_ABLATE 0
+#endif
+
 namespace dba {
 
 namespace {
@@ -155,6 +163,7 @@ k_linearize_v2(const LinParams P) {
   const int gw = R >> 4;                                    // group of the w column
   const int ngroups = N >> 4;
   auto flush = [&](int buf) {
+    if (DBA_V2_ABLATE & 4) return;
     if (warp < 2 || 32 * fq >= R) return;                   // warp-uniform
     for (int g = fj; g < ngroups; g += fnq) {
       if (g > fmaxg && g != gw) continue;                   // warp-uniform
@@ -190,7 +199,7 @@ k_linearize_v2(const LinParams P) {
       if (pn < HW) { eta_n = __ldg(etak + pn); d_n = __ldg(dk + pn); }
     }
     // ---------------- phase 1: the warp's edge, lanes own pixels lane and lane + 32 ---------------------------
-    if (owner) {
+    if (owner && !(DBA_V2_ABLATE & 32)) {
       float Rt[12];
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
@@ -262,7 +271,7 @@ k_linearize_v2(const LinParams P) {
 #ifdef DBA_V2_TRACE
     if (blockIdx.x == 0 && (tid == 0 || tid == 64)) { const long long t_ = clock64(); trw += t_ - tlast; tlast = t_; }
 #endif
-    if (warp < 8) {         // four threads per pixel sum the edges' partials (fixed order), lane 0 of the four stores
+    if (warp < 8 && !(DBA_V2_ABLATE & 16)) {         // four threads per pixel sum the edges' partials (fixed order), lane 0 of the four stores
       const int plr = tid >> 2, part = tid & 3;
       float sum[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
       for (int w = part; w < deg; w += 4) {
@@ -282,7 +291,7 @@ k_linearize_v2(const LinParams P) {
     TR(2);
     __syncthreads();
     TR(3);
-    if (warp < 2) {         // one thread per pixel: Q, w, the source-pose rows
+    if (warp < 2 && !(DBA_V2_ABLATE & 16)) {         // one thread per pixel: Q, w, the source-pose rows
       float sum[5];
 #pragma unroll
       for (int i = 0; i < 5; ++i) sum[i] = ssum[i * T + pl2];
@@ -329,7 +338,7 @@ k_linearize_v2(const LinParams P) {
     __syncthreads();
     TR(5);
     // ---------------- phase 3: operands for the tensor core ----------------------------------------------------
-    {
+    if (!(DBA_V2_ABLATE & 8)) {
       // half a warp per operand row, lane = 4 consecutive pixels = one 16-byte chunk of the swizzled K-major tile:
       // v * sqrt(Q) -> hi = tf32(v), lo = v - hi.  Rows advance by 2 NW (a multiple of 8): constant byte stride.
       const int c16 = lane & 15;
@@ -364,7 +373,7 @@ k_linearize_v2(const LinParams P) {
       const uint32_t acc = tmem + uint32_t(buf * ACC_COLS);
       // the small cross terms first, so that the truncating TMEM adds act on a small accumulator
 #pragma unroll
-      for (int kb = 0; kb < KB; ++kb)
+      for (int kb = 0; kb < ((DBA_V2_ABLATE & 3) ? 0 : KB); ++kb)
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
@@ -377,7 +386,7 @@ k_linearize_v2(const LinParams P) {
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t dh = make_desc_sw128(ah + kb * TILE + ks * 32);
-          mma_tf32_ss(acc, dh, dh, idesc, true);
+          if (!(DBA_V2_ABLATE & 1)) mma_tf32_ss(acc, dh, dh, idesc, (DBA_V2_ABLATE & 2) ? !(kb == 0 && ks == 0) : true);
         }
       mma_commit(&mbar[buf]);
     }
