@@ -24,11 +24,14 @@ using namespace dba;
 
 namespace {
 
+uint64_t g_devbuf_allocs = 0;        // bumped by every (re)allocation: captured CUDA graphs hold the old addresses
+
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
   cudaError_t ensure(size_t bytes, bool zero = false) {
     if (bytes <= cap) return cudaSuccess;
+    ++g_devbuf_allocs;
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
     size_t want = bytes + bytes / 8 + 256;
@@ -141,6 +144,24 @@ struct dba_ctx {
   int opt_p2p_debug = 0;             // timing experiments only: 1 skip the flag wait, 2 skip the sums
   int64_t last_launches = 0;
   size_t smem_cap = 0;
+  // CUDA graphs of whole dba_ba_cached calls (plan hit by key, same buffers and scalars as an earlier call): the
+  // second identical call is captured on `gstream`, later ones are one cudaGraphLaunch on the caller's stream
+  struct BaGraph {
+    const void* ptr[9] = {};         // poses, disps, intr, disps_sens, targets, weights, eta, dx_out, dz_out
+    int64_t dims[8] = {};            // E, N, ht, wd, M, t0, t1, iterations
+    float lm = 0.f, ep = 0.f;
+    bool motion_only = false;
+    uint64_t graph_key = 0, epoch = 0, allocs = 0, last_use = 0;
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;
+    bool failed = false;             // capture or instantiation failed once: this call shape stays on the plain path
+  };
+  std::vector<BaGraph> graphs;
+  uint64_t graph_epoch = 0;          // bumped when the plan or an option changes: every cached graph is stale
+  uint64_t graph_clock = 0;
+  int64_t graph_replays = 0;
+  bool opt_graphs = true;
+  cudaStream_t gstream = nullptr;
 };
 
 namespace {
@@ -187,6 +208,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
     return 0;
   }
   ctx->plan_valid = false;
+  ++ctx->graph_epoch;
   if (E > 0) {
     for (int64_t e = 0; e < E; ++e)
       if (ii[e] < 0 || ii[e] >= N) return fail_arg(ctx, "edge index outside the frame buffer");
@@ -413,7 +435,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
            const float* targets, const float* weights, const float* eta, const int64_t* ii_h, const int64_t* jj_h,
            int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, int iterations, float lm, float ep,
            bool motion_only, float* dx_out, float* dz_out, cudaStream_t st, float* cov_out = nullptr,
-           uint64_t graph_key = 0) {
+           uint64_t graph_key = 0, bool capturing = false) {
   g_launch_count = 0;
   int rc = 0;
   // ii_h == nullptr: the caller's graph key matched the cached plan (plan_hit_by_key), nothing to look at
@@ -425,6 +447,72 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   Workspace ws{};
   rc = ensure_workspace(ctx, ws);
   if (rc) return rc;
+  // ---- whole-call CUDA graph: a call that repeats an earlier one exactly (plan hit by the caller's key, same
+  // buffers, same scalars) is captured once and then replayed with ONE launch.  What this buys is launch latency:
+  // the frontend / motion-only windows are 12-13 dependent kernels of 5-40 us per LM iteration.
+  if (!capturing && ctx->opt_graphs && ii_h == nullptr && E > 0 && graph_key != 0 && cov_out == nullptr &&
+      iterations > 0 && !ctx->profile && !ctx->keep_system && !(ctx->comm != nullptr && ctx->nranks > 1)) {
+    const void* ptr[9] = {poses, disps, intr, disps_sens, targets, weights, eta, dx_out, dz_out};
+    const int64_t dims[8] = {E, N, ht, wd, M, t0, t1, iterations};
+    dba_ctx::BaGraph* hit = nullptr;
+    for (auto it = ctx->graphs.begin(); it != ctx->graphs.end();) {
+      if (it->epoch != ctx->graph_epoch || it->allocs != g_devbuf_allocs) {        // stale: plan / option / workspace changed
+        if (it->exec) cudaGraphExecDestroy(it->exec);
+        it = ctx->graphs.erase(it);
+        continue;
+      }
+      if (it->graph_key == graph_key && it->lm == lm && it->ep == ep && it->motion_only == motion_only &&
+          std::memcmp(it->ptr, ptr, sizeof(ptr)) == 0 && std::memcmp(it->dims, dims, sizeof(dims)) == 0)
+        hit = &*it;
+      ++it;
+    }
+    if (hit != nullptr && hit->exec != nullptr) {
+      hit->last_use = ++ctx->graph_clock;
+      CK(cudaGraphLaunch(hit->exec, st), "graph launch");
+      ++ctx->graph_replays;
+      ctx->last_launches = hit->launches;
+      return 0;
+    }
+    if (hit != nullptr && !hit->failed) {            // second identical call: capture it
+      if (ctx->gstream == nullptr) CK(cudaStreamCreateWithFlags(&ctx->gstream, cudaStreamNonBlocking), "graph stream");
+      cudaGraph_t graph = nullptr;
+      cudaError_t ce = cudaStreamBeginCapture(ctx->gstream, cudaStreamCaptureModeThreadLocal);
+      int crc = 0;
+      if (ce == cudaSuccess) {
+        crc = run_ba(ctx, poses, disps, intr, disps_sens, targets, weights, eta, nullptr, nullptr, E, N, ht, wd, M, t0, t1,
+                     iterations, lm, ep, motion_only, dx_out, dz_out, ctx->gstream, nullptr, graph_key, true);
+        ce = cudaStreamEndCapture(ctx->gstream, &graph);
+      }
+      cudaGraphExec_t exec = nullptr;
+      if (ce == cudaSuccess && crc == 0 && graph != nullptr) ce = cudaGraphInstantiate(&exec, graph, 0);
+      if (graph != nullptr) cudaGraphDestroy(graph);
+      if (ce == cudaSuccess && crc == 0 && exec != nullptr) {
+        hit->exec = exec;
+        hit->launches = ctx->last_launches;
+        hit->last_use = ++ctx->graph_clock;
+        CK(cudaGraphLaunch(exec, st), "graph launch");
+        ++ctx->graph_replays;
+        return 0;
+      }
+      if (exec != nullptr) cudaGraphExecDestroy(exec);
+      cudaGetLastError();                            // the capture failed: this call shape stays on the plain path
+      hit->failed = true;
+      g_launch_count = 0;
+    } else if (hit == nullptr) {                     // first sighting: remember it, run it plainly
+      if (ctx->graphs.size() >= 8) {
+        size_t lru = 0;
+        for (size_t i = 1; i < ctx->graphs.size(); ++i) if (ctx->graphs[i].last_use < ctx->graphs[lru].last_use) lru = i;
+        if (ctx->graphs[lru].exec) cudaGraphExecDestroy(ctx->graphs[lru].exec);
+        ctx->graphs.erase(ctx->graphs.begin() + lru);
+      }
+      dba_ctx::BaGraph ge;
+      std::memcpy(ge.ptr, ptr, sizeof(ptr));
+      std::memcpy(ge.dims, dims, sizeof(dims));
+      ge.lm = lm; ge.ep = ep; ge.motion_only = motion_only; ge.graph_key = graph_key;
+      ge.epoch = ctx->graph_epoch; ge.allocs = g_devbuf_allocs; ge.last_use = ++ctx->graph_clock;
+      ctx->graphs.push_back(ge);
+    }
+  }
   const DeviceGraph& g = ctx->g;
   BAInputs in{poses, disps, intr, disps_sens, targets, weights, eta};
   // sharded: every rank damps its share of H; the constant ep is added once (rank 0)
@@ -628,6 +716,8 @@ void dba_destroy(dba_ctx* c) {
                     &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+  for (auto& ge : c->graphs) if (ge.exec) cudaGraphExecDestroy(ge.exec);
+  if (c->gstream) cudaStreamDestroy(c->gstream);
   if (c->side) cudaStreamDestroy(c->side);
   if (c->side2) cudaStreamDestroy(c->side2);
   if (c->ev_join2) cudaEventDestroy(c->ev_join2);
@@ -642,7 +732,9 @@ const char* dba_last_error(dba_ctx* c) { return c ? c->err.c_str() : "null conte
 int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   if (!ctx || !name) return -1;
   std::string n(name);
-  if (n == "block_diag_quirk") ctx->block_diag_quirk = value != 0;
+  ++ctx->graph_epoch;                // any option may change what a call launches: cached call graphs are stale
+  if (n == "cuda_graphs") ctx->opt_graphs = value != 0;
+  else if (n == "block_diag_quirk") ctx->block_diag_quirk = value != 0;
   else if (n == "keep_system") ctx->keep_system = value != 0;
   else if (n == "profile") { ctx->profile = value != 0; for (double& v : ctx->stage_ms) v = 0; }
   else if (n == "multilaunch_cholesky") ctx->opt_multilaunch_chol = value != 0;
@@ -1190,6 +1282,11 @@ int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t c
     if (cap < int64_t(sizeof(d))) return -1;
     std::memcpy(host_out, d, sizeof(d));
     return sizeof(d);
+  }
+  if (n == "graph_replays") {
+    if (cap < int64_t(sizeof(int64_t))) return -1;
+    std::memcpy(host_out, &ctx->graph_replays, sizeof(int64_t));
+    return sizeof(int64_t);
   }
   if (n == "stage_ms") {
     if (cap < int64_t(sizeof(ctx->stage_ms))) return -1;

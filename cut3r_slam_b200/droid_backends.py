@@ -463,6 +463,17 @@ def last_launch_count(device=None, _ctx=None):
     return int(ctx.lib.dba_last_launch_count(ctx.handle))
 
 
+def graph_replays(device=None, _ctx=None):
+    """How many `ba` calls of this context ran as ONE cudaGraphLaunch (a call that repeats an earlier one exactly --
+    same edge-list tensors, same buffers, same scalars -- is captured on its second occurrence and replayed from then
+    on; option "cuda_graphs" 0 turns that off)."""
+    ctx = _ctx if _ctx is not None else context(device)
+    buf = (C.c_int64 * 1)()
+    if ctx.lib.dba_debug_read(ctx.handle, b"graph_replays", buf, C.sizeof(buf)) < 0:
+        ctx.check(-1)
+    return int(buf[0])
+
+
 STAGES = ("linearize", "assemble", "allreduce", "cholesky", "backsub", "retract")
 
 

@@ -39,7 +39,10 @@ const char* dba_version(void);
  * out-degree <= 20 (default 1); "refine" 0/1/2 -- iterative refinement of the pose solve: off / last iteration of a call /
  * every iteration (default 1); "cholesky_tc" n -- 128-column-panel factorisation with tcgen05 trailing update from system
  * size n on (default 0 = off); "p2p_allreduce" 0/1, "p2p_max_n"; "stream_inputs" -1/0/1; "wide_tensor_cores" 0/1/2 -- keyframes with
- * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2). */
+ * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2);
+ * "cuda_graphs" 0/1 -- dba_ba_cached calls that repeat an earlier call exactly (plan hit by graph_key, same buffer
+ * addresses, sizes, iterations, lm, ep) are captured into a CUDA graph on their second occurrence and replayed with one
+ * cudaGraphLaunch on `stream` afterwards (default 1; not under "profile" / "keep_system", not for sharded contexts). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
 
 /* ---- ba: replaces droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
@@ -213,7 +216,8 @@ int dba_comm_p2p_import(dba_ctx* ctx, const void* handles /* [nranks][64] */, in
 
 /* ---- test / profiling hooks */
 /* name: "system" -> [(n6+1)*ld] floats of the last assembled reduced system (needs keep_system=1),
- * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; "stage_ms" -> double[8] accumulated
+ * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; "graph_replays" -> int64 calls that ran as one
+ * cudaGraphLaunch; "stage_ms" -> double[8] accumulated
  * {linearize, assemble, allreduce, cholesky+solve, backsub, retract, 0, LM iterations}; returns the number of BYTES
  * written (<= cap) or <0. Synchronous. */
 int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t cap);

@@ -369,3 +369,39 @@ def test_hub_keyframe_next_to_tensor_core_keyframes():
     gap = rel_err(infos32[0][0], infos[0][0])
     assert rel_err(dx.cpu(), infos[0][0]) < MULT * gap + 1e-5, gap
     assert rel_err(g[1].cpu(), ref_d) < 1e-4
+
+
+def test_cuda_graph_replay_is_bit_identical():
+    """A `ba` call that repeats an earlier one exactly (same edge-list tensors, same buffers, same scalars) is captured
+    into a CUDA graph on its second occurrence and replayed afterwards (dba_api.cu run_ba): same kernels, same order,
+    so poses / disps / dx / dz must equal the plain path bit for bit; an option change drops the cached graphs."""
+    db = _db()
+    p = make_problem("frontend")
+    db.set_option("cuda_graphs", 0)
+    a = p.to("cuda")
+    ref_dx, ref_dz = db.ba(*a.ba_args())
+    db.set_option("cuda_graphs", 1)
+    g = p.to("cuda")
+    args = g.ba_args()
+    poses0, disps0 = g.poses.clone(), g.disps.clone()
+    r0 = db.graph_replays()
+    outs = []
+    for k in range(8):
+        g.poses.copy_(poses0)
+        g.disps.copy_(disps0)
+        outs.append(db.ba(*args))            # kept alive: the output buffers of later calls are new addresses ...
+        if k >= 3:
+            outs.pop(0)                      # ... until the allocator hands the first ones back
+        dx, dz = outs[-1]
+        assert torch.equal(g.poses, a.poses) and torch.equal(g.disps, a.disps), k
+        assert torch.equal(dx, ref_dx) and torch.equal(dz, ref_dz), k
+    assert db.graph_replays() > r0
+    db.set_option("refine", 0)               # any option change invalidates the cached graphs
+    try:
+        g.poses.copy_(poses0)
+        g.disps.copy_(disps0)
+        n = db.graph_replays()
+        db.ba(*args)
+        assert db.graph_replays() == n
+    finally:
+        db.set_option("refine", 1)
