@@ -1,7 +1,9 @@
 """Refresh profiles/linearize_traffic.json from an `ncu --set full` capture of ONE LM iteration's linearize launches
-(bench.py reads it for roofline.traffic).  usage: python tools/ncu_traffic.py report.ncu-rep workload@ngpus"""
+(bench.py reads it for roofline.traffic).
+usage: python tools/ncu_traffic.py report.ncu-rep workload@ngpus [LM iterations in the capture, default 1]"""
 import csv, io, json, os, subprocess, sys
 rep, key = sys.argv[1], sys.argv[2]
+niter = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 h, units = rows[0], rows[1]
@@ -17,6 +19,7 @@ for r in rows[2:]:
     print(d["Kernel Name"][:70], d["gpu__time_duration.sum"], u["gpu__time_duration.sum"])
 path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "linearize_traffic.json")
 rec = json.load(open(path)) if os.path.exists(path) else {}
+tot /= niter
 rec[key] = int(tot)
 rec["_source"] = rec.get("_source", {})
 rec["_source"][key] = os.path.basename(rep)
