@@ -264,10 +264,19 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
       const int njobs = int(degs.size() + 2 * wide.size());
       int cand_lo = 1;
       while (cand_lo < ntilesT && (ntilesT + cand_lo - 1) / cand_lo > 2 && njobs * cand_lo < 3 * slots) ++cand_lo;
-      for (int cand = cand_lo; cand <= 52 && cand <= ntilesT; ++cand) {
-        const int tps_c = (ntilesT + cand - 1) / cand, S_c = (ntilesT + tps_c - 1) / tps_c;
-        if (S_c != cand && cand != cand_lo) continue;
-        if (S_c != cand) { continue; }
+      // small windows (frontend: 12 keyframes): when the whole stage fits ONE wave of CTAs with a handful of tiles each,
+      // that beats the multi-wave splits above (measured, frontend: S = 26 -> 0.162 ms per call, S = 12 = one wave ->
+      // 0.130 ms, S = 13 = 156 CTAs -> 0.148 ms); the simulation decides
+      int one_wave = 0;
+      if (use_v2 && njobs > 0 && njobs * cand_lo > slots && slots / njobs >= 1) {
+        const int s1 = std::min(slots / njobs, ntilesT);
+        const int tps1 = (ntilesT + s1 - 1) / s1;
+        if (tps1 <= 6) one_wave = (ntilesT + tps1 - 1) / tps1;
+      }
+      for (int cand = (one_wave > 0 ? cand_lo - 1 : cand_lo); cand <= 52 && cand <= ntilesT; ++cand) {
+        const int cand_s = (cand < cand_lo) ? one_wave : cand;       // the extra first round tries the one-wave split
+        const int tps_c = (ntilesT + cand_s - 1) / cand_s, S_c = (ntilesT + tps_c - 1) / tps_c;
+        if (S_c != cand_s) { continue; }
         std::priority_queue<double, std::vector<double>, std::greater<double>> free_at;
         for (int i = 0; i < slots; ++i) free_at.push(0.0);
         double makespan = 0.0;

@@ -333,6 +333,11 @@ def test_tensor_core_cholesky_agrees(P, E):
     db = _db()
     p = make_problem(P=P, E=E, ht=20, wd=24, iters=2, t0=2, r=4, seed=81)
     db.set_option("refine", 0)
+    # The pixel-split count is pinned: this experimental factorisation amplifies the summation-order noise of the
+    # reduced system (measured at P = 40, tools/diag_tc_cholesky_case.py: disps error 4.6e-5 .. 1.4e-4 over splits
+    # 1..8 against 3.1e-5 .. 4.4e-5 for the shipped cooperative kernel, reference fp32 gap 2.8e-5) -- one more reason
+    # it stays off (profiles/r2_cholesky_tc.md).  The shipped path's tests run with the plan's own split choice.
+    db.set_option("splits", 4)
     try:
         a = p.to("cuda")
         db.ba(*a.ba_args())
@@ -342,6 +347,7 @@ def test_tensor_core_cholesky_agrees(P, E):
     finally:
         db.set_option("cholesky_tc", 0)
         db.set_option("refine", 1)
+        db.set_option("splits", 0)
     assert rel_err(b.disps.cpu(), a.disps.cpu()) < 2e-4
     assert float((b.poses - a.poses).abs().max()) < 1e-4
     ref_p, ref_d = od.oracle_ba(*p.ba_args(), dtype=torch.float64)
