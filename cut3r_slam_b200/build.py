@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libdba.so")
 STAMP = os.path.join(HERE, "csrc", ".build_stamp")
 
-SOURCES = ["dba_api.cu", "dba_linearize.cu", "dba_linearize_tc.cu", "dba_linearize_v2.cu", "dba_assemble.cu", "dba_chol.cu", "dba_chol_fused.cu", "dba_refine.cu", "dba_p2p.cu", "dba_pgba.cu", "dba_companion.cu", "dba_jdsa.cu", "dba_glue.cu", "dba_cov.cu", "dba_relpose.cu", "dba_plan.cpp", "dba_graph.cpp"]
+SOURCES = ["dba_api.cu", "dba_linearize.cu", "dba_linearize_tc.cu", "dba_linearize_v2.cu", "dba_assemble.cu", "dba_chol.cu", "dba_chol_fused.cu", "dba_refine.cu", "dba_trisolve_cluster.cu", "dba_p2p.cu", "dba_pgba.cu", "dba_companion.cu", "dba_jdsa.cu", "dba_glue.cu", "dba_cov.cu", "dba_relpose.cu", "dba_plan.cpp", "dba_graph.cpp"]
 HEADERS = ["dba_kernels.h", "dba_math.cuh", "dba_linearize.cuh", "dba_umma.cuh", "dba_plan.h", os.path.join("..", "..", "include", "dba.h")]
 
 NVCC_FLAGS = [

@@ -757,6 +757,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "p2p_debug") ctx->opt_p2p_debug = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
+  else if (n == "cluster_solve") g_cluster_solve_mode = int(value);
   else if (n == "splits") { ctx->opt_splits = int(value); ctx->plan_valid = false; }
   else if (n == "ppl") {
     int v = int(value);

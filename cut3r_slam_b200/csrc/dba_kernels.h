@@ -163,6 +163,11 @@ cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const 
                         float* scales, const float* disps_in, const float* scales_in, const int32_t* kx, int M, int N, int ht, int wd, int hs, int ws, float alpha,
                         float ep, float lm, float* dzcov, float* dz_out, float* dso_out, cudaStream_t st);
 
+// triangular solves on one thread-block cluster with the factor resident in distributed shared memory
+// (dba_trisolve_cluster.cu, n <= 768); cudaErrorNotSupported -> the caller uses the single-CTA kernels
+extern int g_cluster_solve_mode;
+cudaError_t launch_trisolve_cluster(const Workspace& ws, int n, bool forward, int mode, cudaStream_t st);
+
 // dba_ctx accessors (dba_api.cu) for entry points that live beside their kernels
 int ctx_device(::dba_ctx* c);
 int ctx_fail_arg(::dba_ctx* c, const char* m);

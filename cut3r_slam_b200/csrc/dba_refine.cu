@@ -109,6 +109,11 @@ cudaError_t launch_refine(const Workspace& ws, const float* Sorig, int n, cudaSt
   float* yr = ws.Lm + int64_t(n) * ws.ldA;
   k_residual<<<(n + 7) / 8, 256, 0, st>>>(Sorig, ws.dx, ws.ldA, n, yr);
   g_launch_count++;
+  {
+    const cudaError_t ce = launch_trisolve_cluster(ws, n, true, 0, st);
+    if (ce == cudaSuccess) return launch_backsolve(ws, n, 3, st);
+    if (ce != cudaErrorNotSupported) return ce;
+  }
   int stride = 0, linv = 0;
   cholesky_ldiag_layout(&stride, &linv);
   const size_t smem = (size_t((n + NB + 3) & ~3) + NB * (NB + 1) + NB) * sizeof(float);
