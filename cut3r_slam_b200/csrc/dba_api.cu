@@ -101,7 +101,7 @@ struct dba_ctx {
   DevBuf d_plan_i32, d_items;
   DeviceGraph g{};
   // workspace
-  DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep;
+  DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep, solve_msg, solve_flag;
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
   bool opt_multilaunch_chol = false;
   bool opt_tc = true;
@@ -436,6 +436,11 @@ int ensure_workspace(dba_ctx* ctx, Workspace& ws) {
   ws.Q = ctx->Q.as<float>(); ws.w = ctx->w.as<float>(); ws.Hblk = ctx->Hblk.as<float>(); ws.vblk = ctx->vblk.as<float>();
   ws.A = ctx->A.as<float>(); ws.Lm = ctx->Lm.as<float>(); ws.ldA = ld; ws.Ldiag = ctx->Ldiag.as<float>(); ws.dx = ctx->dx.as<float>();
   ws.dz = ctx->dz.as<float>(); ws.fail = ctx->fail.as<int>();
+  if (trisolve_grid_msg_floats(P.n6) > 0) {          // message slots of the grid-chain triangular solves (n > 768)
+    CK(ctx->solve_msg.ensure(trisolve_grid_msg_floats(P.n6) * f), "workspace");
+    CK(ctx->solve_flag.ensure(trisolve_grid_flag_words(P.n6) * sizeof(unsigned), true), "workspace");
+    ws.solve_msg = ctx->solve_msg.as<float>(); ws.solve_flag = ctx->solve_flag.as<unsigned>();
+  }
   return 0;
 }
 
@@ -719,7 +724,7 @@ void dba_destroy(dba_ctx* c) {
   cudaSetDevice(c->device);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
-                    &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->s_poses, &c->s_disps, &c->s_intr,
+                    &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->d_pack, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
                     &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
                     &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep};

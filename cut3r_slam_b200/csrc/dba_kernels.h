@@ -55,6 +55,8 @@ struct Workspace {
   float* dx;       // [Pp,6]
   float* dz;       // [M,HW]
   int* fail;       // [4]: [0] failed-factorisation flag, [1] grid-barrier counter (both self-resetting)
+  float* solve_msg = nullptr;      // n > 768: [NC][NC][64] message slots of the grid-chain triangular solves
+  unsigned* solve_flag = nullptr;  // ... [NC][NC] flags + the epoch counter (zeroed once)
 };
 
 // linearisation + Schur products; picks the pixel-tile width from degmax. Returns cudaError_t.
@@ -167,6 +169,8 @@ cudaError_t launch_jdsa(float* disps, const float* Cin, const float* win, const 
 // (dba_trisolve_cluster.cu, n <= 768); cudaErrorNotSupported -> the caller uses the single-CTA kernels
 extern int g_cluster_solve_mode;
 cudaError_t launch_trisolve_cluster(const Workspace& ws, int n, bool forward, int mode, cudaStream_t st);
+size_t trisolve_grid_msg_floats(int n);
+size_t trisolve_grid_flag_words(int n);
 
 // dba_ctx accessors (dba_api.cu) for entry points that live beside their kernels
 int ctx_device(::dba_ctx* c);
