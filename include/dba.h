@@ -42,7 +42,9 @@ const char* dba_version(void);
  * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2);
  * "cuda_graphs" 0/1 -- dba_ba_cached calls that repeat an earlier call exactly (plan hit by graph_key, same buffer
  * addresses, sizes, iterations, lm, ep) are captured into a CUDA graph on their second occurrence and replayed with one
- * cudaGraphLaunch on `stream` afterwards (default 1; not under "profile" / "keep_system", not for sharded contexts). */
+ * cudaGraphLaunch on `stream` afterwards (default 1; not under "profile" / "keep_system", not for sharded contexts);
+ * "cluster_solve" 0/1 -- triangular solves as a panel chain through one thread-block cluster (n <= 768) or a
+ * co-resident grid (larger n) instead of the single-CTA slab kernels (default 1; process-wide). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
 
 /* ---- ba: replaces droid_backends.ba(poses, disps, intrinsics, disps_sens, targets, weights, eta,
