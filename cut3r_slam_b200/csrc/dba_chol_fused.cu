@@ -258,7 +258,11 @@ __device__ __forceinline__ void diag_stage(CholSmem& S, float* A, float* Lm, flo
   TRACE(0, 11);
 }
 
-__global__ void __launch_bounds__(NTH)
+// MINB = 2 (n >= 1024): 128 registers with ~170 bytes of spills so that two CTAs share an SM and cover each other's tile
+// loads (n = 3060: 1452 -> 1374 us); MINB = 1 (200 registers, no spills) where the look-ahead CTA's chain is the step
+// (n = 756: the two-CTA build costs 9 us per factorisation in the pipeline)
+template <int MINB>
+__global__ void __launch_bounds__(NTH, MINB)
 k_chol_fused(float* A, float* Lm, float* Ldiag, int ld, int n, int* fail, unsigned* bar) {
   __shared__ CholSmem S;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -686,7 +690,8 @@ cudaError_t launch_cholesky_coop(const Workspace& ws, int n, int max_ctas, cudaS
   unsigned* bar = reinterpret_cast<unsigned*>(ws.fail + 1);
   float* dx = ws.dx;
   void* args[] = {&A, &Lm, &Ldiag, &ld, &n, &fail, &bar};
-  cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_chol_fused), dim3(grid), dim3(NTH), args, 0, st);
+  void* kern = (n >= 1024) ? reinterpret_cast<void*>(k_chol_fused<2>) : reinterpret_cast<void*>(k_chol_fused<1>);
+  cudaError_t err = cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(NTH), args, 0, st);
   g_launch_count++;
   if (err != cudaSuccess) return err;
   return launch_backsolve(ws, n, finalize ? 1 : 0, st);
@@ -739,7 +744,9 @@ int cholesky_coop_max_ctas(int n) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
   if (!coop || n > 9000) return 0;      // k_backsolve keeps x in shared memory
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_chol_fused, NTH, 0) != cudaSuccess || per < 1) return 0;
+  const cudaError_t oe = (n >= 1024) ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_chol_fused<2>, NTH, 0)
+                                     : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_chol_fused<1>, NTH, 0);
+  if (oe != cudaSuccess || per < 1) return 0;
   return sms * (per > 2 ? 2 : per);
 }
 
