@@ -68,5 +68,55 @@ def build(force=False, verbose=False):
     return OUT
 
 
+EXT_DIR = os.path.join(HERE, "ext")
+EXT_SRC = os.path.join(CSRC, "droid_backends_ext.cpp")
+EXT_STAMP = os.path.join(CSRC, ".ext_build_stamp")
+
+
+def ext_path():
+    import sysconfig
+    return os.path.join(EXT_DIR, "droid_backends" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_ext(force=False):
+    """The compiled `droid_backends` torch extension (csrc/droid_backends_ext.cpp) over libdba, in-tree at
+    cut3r_slam_b200/ext/ (import it with that directory on sys.path: the reference's module name).  One g++ call with
+    torch's own include / library paths; rpath $ORIGIN/.. finds libdba.so, torch's libraries are already loaded by
+    `import torch`."""
+    import sysconfig
+    from torch.utils import cpp_extension as ce
+    build()
+    out = ext_path()
+    h = hashlib.sha256()
+    for f in (EXT_SRC, os.path.join(HERE, "..", "include", "dba.h")):
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    import torch
+    h.update(torch.__version__.encode())
+    dig = h.hexdigest()
+    if not force and os.path.exists(out) and os.path.exists(EXT_STAMP) and open(EXT_STAMP).read().strip() == dig:
+        return out
+    os.makedirs(EXT_DIR, exist_ok=True)
+    cxx = os.environ.get("CXX", "g++")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=droid_backends",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", "-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI)]
+    for inc in ce.include_paths("cuda") + [sysconfig.get_paths()["include"], os.path.join(HERE, "..", "include")]:
+        cmd += ["-I", inc]
+    cmd += [EXT_SRC, "-o", out]
+    for lp in ce.library_paths("cuda"):
+        cmd += ["-L", lp]
+    cmd += ["-L", HERE, "-ldba", "-lc10", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10_cuda", "-ltorch_cuda", "-lcudart",
+            "-Wl,-rpath,$ORIGIN/..", "-Wl,--no-as-needed"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("building the droid_backends extension failed")
+    with open(EXT_STAMP, "w") as fh:
+        fh.write(dig)
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--ext" in sys.argv:
+        print(build_ext(force="--force" in sys.argv))
