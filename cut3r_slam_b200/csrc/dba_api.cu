@@ -139,6 +139,7 @@ struct dba_ctx {
   P2PPeers p2p_peers{};
   bool p2p_ok = false;
   bool opt_p2p = true;
+  bool opt_p2p_two_shot = true;      // n > p2p_max_n: reduce-scatter + all-gather over peer memory instead of NCCL
   int opt_p2p_max_n = 1536;          // larger systems are bandwidth-bound: NCCL's reduce-scatter + all-gather moves less
   uint32_t p2p_epoch = 0;
   int opt_p2p_debug = 0;             // timing experiments only: 1 skip the flag wait, 2 skip the sums
@@ -581,18 +582,24 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     }
     mark();
     const bool sharded = ctx->comm != nullptr && ctx->nranks > 1;
-    const bool use_p2p = sharded && ctx->p2p_ok && ctx->opt_p2p && g.n6 <= ctx->opt_p2p_max_n &&
-                         size_t(g.n6 + 1) * ws.ldA <= ctx->p2p_slab_floats;
+    const bool p2p_fits = sharded && ctx->p2p_ok && ctx->opt_p2p && size_t(g.n6 + 1) * ws.ldA <= ctx->p2p_slab_floats;
+    const bool two_shot = p2p_fits && g.n6 > ctx->opt_p2p_max_n && ctx->opt_p2p_two_shot;
+    const bool use_p2p = (p2p_fits && g.n6 <= ctx->opt_p2p_max_n) || two_shot;
     if (use_p2p) {
       // the rank's share goes into its exchange slab; ONE kernel signals, waits and sums all ranks' lower triangles
+      // (large systems: reduce-scatter + all-gather over the same slabs, dba_p2p.cu)
       ++ctx->p2p_epoch;
       const int parity = int(ctx->p2p_epoch & 1u);
       Workspace wsx = ws;
       wsx.A = ctx->p2p_buf + size_t(parity) * ctx->p2p_slab_floats;
       CK(launch_assemble(g, in, wsx, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
       mark();
-      CK(launch_p2p_allreduce(ctx->p2p_peers, ctx->nranks, ctx->rank, ctx->p2p_slab_floats, 2 * ctx->p2p_slab_floats,
-                              parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, ctx->opt_p2p_debug, st), "all-reduce (peer memory)");
+      if (two_shot)
+        CK(launch_p2p_allreduce_two_shot(ctx->p2p_peers, ctx->nranks, ctx->rank, ctx->p2p_slab_floats, 3 * ctx->p2p_slab_floats,
+                                         parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, st), "all-reduce (peer memory, two-shot)");
+      else
+        CK(launch_p2p_allreduce(ctx->p2p_peers, ctx->nranks, ctx->rank, ctx->p2p_slab_floats, 3 * ctx->p2p_slab_floats,
+                                parity, ctx->p2p_epoch, ws.ldA, g.n6, ws.A, ws.fail + 2, ctx->opt_p2p_debug, st), "all-reduce (peer memory)");
     } else {
     CK(launch_assemble(g, in, ws, lm, ep_eff, 0.f, motion_only, ctx->block_diag_quirk && motion_only, st), "assemble");
     mark();
@@ -759,6 +766,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "refine") ctx->opt_refine = int(value);
   else if (n == "p2p_allreduce") ctx->opt_p2p = value != 0;
   else if (n == "p2p_max_n") ctx->opt_p2p_max_n = int(value);
+  else if (n == "p2p_two_shot") ctx->opt_p2p_two_shot = value != 0;
   else if (n == "p2p_debug") ctx->opt_p2p_debug = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
@@ -1241,8 +1249,9 @@ int dba_comm_p2p_export(dba_ctx* ctx, void* handle64_out, int64_t slab_bytes) {
   if (ctx->p2p_buf) { cudaFree(ctx->p2p_buf); ctx->p2p_buf = nullptr; ctx->p2p_ok = false; }
   const size_t slab_floats = (size_t(slab_bytes) / 4 + 3) & ~size_t(3);
   void* p = nullptr;
-  CK(cudaMalloc(&p, (2 * slab_floats + 64) * sizeof(float)), "p2p buffer");
-  CK(cudaMemset(p, 0, (2 * slab_floats + 64) * sizeof(float)), "p2p buffer");
+  // two slabs (alternating by epoch), the reduced rows of the two-shot path, two flag arrays
+  CK(cudaMalloc(&p, (3 * slab_floats + 64) * sizeof(float)), "p2p buffer");
+  CK(cudaMemset(p, 0, (3 * slab_floats + 64) * sizeof(float)), "p2p buffer");
   CK(cudaDeviceSynchronize(), "p2p buffer");
   cudaIpcMemHandle_t h;
   cudaError_t e = cudaIpcGetMemHandle(&h, p);

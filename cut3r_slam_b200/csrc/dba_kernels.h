@@ -117,6 +117,10 @@ struct P2PPeers { float* base[8]; };     // every rank's exchange buffer as mapp
 cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats,
                                  int parity, uint32_t epoch, int ld, int n, float* out, int* err, int debug, cudaStream_t st);
 
+cudaError_t launch_p2p_allreduce_two_shot(const P2PPeers& peers, int nranks, int rank, size_t slab_floats,
+                                          size_t flags_off_floats, int parity, uint32_t epoch, int ld, int n, float* out,
+                                          int* err, cudaStream_t st);
+
 // pgba: Sim3 pose-graph BA (dba_pgba.cu); all device pointers, the plan arrays as uploaded for the 6-dof path
 struct PgbaArgs {
   float* poses;              // [N,8] Sim3, in place

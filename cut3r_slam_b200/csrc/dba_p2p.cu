@@ -77,6 +77,91 @@ k_p2p_allreduce(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t
   }
 }
 
+// ---- two-shot all-reduce for the LARGE systems (n > p2p_max_n: loop-closure graphs, 18.8 MB of triangle at n = 3060).
+// The one-shot kernel makes every rank read all N slabs (N x 18.8 MB inbound: slower than NCCL's ring).  Here the rows
+// are cut into N ranges of equal element count; (A) rank r sums ITS rows over all slabs, in rank order, into the `red`
+// region of its own exchange buffer; (B) every rank copies the N reduced ranges into its private system matrix.
+// Inbound per rank: 2 (N - 1) / N of the triangle (33 MB at N = 8) and two flag round trips; the sum of a row is formed
+// on ONE rank, so all ranks hold the same bits.  Ordering: `red` is rewritten by A(e + 1) only after every peer's slab
+// flag e + 1 was seen, which a peer raises after its B(e) finished reading; slabs alternate by epoch as above.
+struct P2PRows { int b[9]; };            // rows [b[r], b[r + 1]) belong to rank r (row n = the rhs row)
+
+__device__ __forceinline__ bool p2p_wait_flags(const uint32_t* f, uint32_t epoch) {
+  const long long t0 = clock64();
+  while (int32_t(*reinterpret_cast<const volatile uint32_t*>(f) - epoch) < 0) {
+    __nanosleep(200);
+    if (clock64() - t0 > 6000000000LL) return false;
+  }
+  (void)ld_acquire_sys(f);
+  return true;
+}
+
+__global__ void __launch_bounds__(256)
+k_p2p_reduce_scatter(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats, int parity,
+                     uint32_t epoch, int ld, int n, P2PRows rows, int* __restrict__ err) {
+  __shared__ int s_bad;
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid == 0) s_bad = 0;
+  if (blockIdx.x == 0 && tid < nranks) {            // the previous kernel on this stream wrote my slab
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(peers.base[tid] + flags_off_floats) + rank, epoch);
+  }
+  __syncthreads();
+  if (tid < nranks && !p2p_wait_flags(reinterpret_cast<const uint32_t*>(peers.base[rank] + flags_off_floats) + tid, epoch)) s_bad = 1;
+  __syncthreads();
+  if (s_bad && tid == 0) *err = 1;
+  const int gw = blockIdx.x * 8 + (tid >> 5), nw = gridDim.x * 8;
+  const size_t soff = size_t(parity) * slab_floats;
+  float* red = peers.base[rank] + 2 * slab_floats;
+  for (int i = rows.b[rank + 1] - 1 - gw; i >= rows.b[rank]; i -= nw) {
+    const int ncol = (i < n) ? i + 1 : n;
+    const size_t roff = size_t(i) * ld;
+    for (int c4 = lane * 4; c4 < ncol; c4 += 128) {
+      float4 v[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < nranks) v[r] = ld_peer(reinterpret_cast<const float4*>(peers.base[r] + soff + roff + c4));
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < nranks) { a.x += v[r].x; a.y += v[r].y; a.z += v[r].z; a.w += v[r].w; }
+      *reinterpret_cast<float4*>(red + roff + c4) = a;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_p2p_allgather(P2PPeers peers, int nranks, int rank, size_t slab_floats, size_t flags_off_floats, uint32_t epoch, int ld,
+                int n, P2PRows rows, float* __restrict__ out, int* __restrict__ err) {
+  __shared__ int s_bad;
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid == 0) s_bad = 0;
+  if (blockIdx.x == 0 && tid < nranks) {            // the previous kernel on this stream wrote my reduced rows
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(peers.base[tid] + flags_off_floats) + 16 + rank, epoch);
+  }
+  __syncthreads();
+  if (tid < nranks && !p2p_wait_flags(reinterpret_cast<const uint32_t*>(peers.base[rank] + flags_off_floats) + 16 + tid, epoch)) s_bad = 1;
+  __syncthreads();
+  if (s_bad && tid == 0) *err = 1;
+  const int gw = blockIdx.x * 8 + (tid >> 5), nw = gridDim.x * 8;
+  for (int i = n - gw; i >= 0; i -= nw) {
+    int q = 0;
+    while (q + 1 < nranks && i >= rows.b[q + 1]) ++q;
+    const int ncol = (i < n) ? i + 1 : n;
+    const float* src = peers.base[q] + 2 * slab_floats + size_t(i) * ld;
+    float* dst = out + size_t(i) * ld;
+    for (int c4 = lane * 4; c4 < ncol; c4 += 256) {
+      const bool two = c4 + 128 < ncol;
+      const float4 a0 = ld_peer(reinterpret_cast<const float4*>(src + c4));
+      float4 a1 = a0;
+      if (two) a1 = ld_peer(reinterpret_cast<const float4*>(src + c4 + 128));
+      *reinterpret_cast<float4*>(dst + c4) = a0;
+      if (two) *reinterpret_cast<float4*>(dst + c4 + 128) = a1;
+    }
+  }
+}
+
 // NCCL path of the large systems: only the lower triangle + rhs row carry data, so they are packed into a contiguous
 // buffer (row i at i (i + 1) / 2, the rhs row behind the triangle), all-reduced and unpacked: half the bytes on NVLink.
 template <bool PACK>
@@ -101,6 +186,32 @@ cudaError_t launch_p2p_allreduce(const P2PPeers& peers, int nranks, int rank, si
   int grid = (n + 1 + 7) / 8;
   if (grid > 296) grid = 296;
   k_p2p_allreduce<<<grid, 256, 0, st>>>(peers, nranks, rank, slab_floats, flags_off_floats, parity, epoch, ld, n, out, err, debug);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
+// rows cut into nranks ranges of (nearly) equal element count; two launches on `st`
+cudaError_t launch_p2p_allreduce_two_shot(const P2PPeers& peers, int nranks, int rank, size_t slab_floats,
+                                          size_t flags_off_floats, int parity, uint32_t epoch, int ld, int n, float* out,
+                                          int* err, cudaStream_t st) {
+  P2PRows rows;
+  const double total = double(n) * (n + 1) / 2 + n;
+  int q = 1;
+  double acc = 0.0;
+  rows.b[0] = 0;
+  for (int i = 0; i <= n && q < nranks; ++i) {
+    acc += (i < n) ? double(i + 1) : double(n);
+    while (q < nranks && acc >= total * q / nranks) rows.b[q++] = i + 1;
+  }
+  for (; q <= 8; ++q) rows.b[q] = n + 1;
+  for (int r = nranks; r <= 8; ++r) rows.b[r] = n + 1;
+  int grid = (n + 1 + 7) / 8;
+  if (grid > 296) grid = 296;
+  int gridA = ((n + 1) / nranks + 7) / 8 + 1;
+  if (gridA > 296) gridA = 296;
+  k_p2p_reduce_scatter<<<gridA, 256, 0, st>>>(peers, nranks, rank, slab_floats, flags_off_floats, parity, epoch, ld, n, rows, err);
+  g_launch_count++;
+  k_p2p_allgather<<<grid, 256, 0, st>>>(peers, nranks, rank, slab_floats, flags_off_floats, epoch, ld, n, rows, out, err);
   g_launch_count++;
   return cudaGetLastError();
 }

@@ -56,7 +56,7 @@ class ShardedBA:
         self.ctx = droid_backends._Ctx(idx)
         self.rank, self.nranks = 0, 1
 
-    def init_comm(self, p2p=True, p2p_slab_bytes=16 << 20):
+    def init_comm(self, p2p=True, p2p_slab_bytes=40 << 20):
         import torch.distributed as dist
         self.rank, self.nranks = dist.get_rank(), dist.get_world_size()
         if self.nranks == 1:
