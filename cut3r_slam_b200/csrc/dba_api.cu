@@ -139,7 +139,8 @@ struct dba_ctx {
   P2PPeers p2p_peers{};
   bool p2p_ok = false;
   bool opt_p2p = true;
-  bool opt_p2p_two_shot = true;      // n > p2p_max_n: reduce-scatter + all-gather over peer memory instead of NCCL
+  int opt_p2p_two_shot = 1;          // n > p2p_max_n: reduce-scatter + all-gather over peer memory instead of NCCL:
+                                     // 0 never, 1 for two ranks (where it measured faster), 2 always
   int opt_p2p_max_n = 1536;          // larger systems are bandwidth-bound: NCCL's reduce-scatter + all-gather moves less
   uint32_t p2p_epoch = 0;
   int opt_p2p_debug = 0;             // timing experiments only: 1 skip the flag wait, 2 skip the sums
@@ -583,7 +584,10 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     mark();
     const bool sharded = ctx->comm != nullptr && ctx->nranks > 1;
     const bool p2p_fits = sharded && ctx->p2p_ok && ctx->opt_p2p && size_t(g.n6 + 1) * ws.ldA <= ctx->p2p_slab_floats;
-    const bool two_shot = p2p_fits && g.n6 > ctx->opt_p2p_max_n && ctx->opt_p2p_two_shot;
+    // measured on loopclosure (n = 3060): 2 GPUs 17.69 ms against 18.05 with the packed ncclAllReduce; 4 GPUs 14.53
+    // against 14.34, 8 GPUs 13.64 against 13.32 (NCCL reduces inside the switch there): on by default for two ranks
+    const bool two_shot = p2p_fits && g.n6 > ctx->opt_p2p_max_n &&
+                          (ctx->opt_p2p_two_shot >= 2 || (ctx->opt_p2p_two_shot == 1 && ctx->nranks <= 2));
     const bool use_p2p = (p2p_fits && g.n6 <= ctx->opt_p2p_max_n) || two_shot;
     if (use_p2p) {
       // the rank's share goes into its exchange slab; ONE kernel signals, waits and sums all ranks' lower triangles
@@ -766,7 +770,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "refine") ctx->opt_refine = int(value);
   else if (n == "p2p_allreduce") ctx->opt_p2p = value != 0;
   else if (n == "p2p_max_n") ctx->opt_p2p_max_n = int(value);
-  else if (n == "p2p_two_shot") ctx->opt_p2p_two_shot = value != 0;
+  else if (n == "p2p_two_shot") ctx->opt_p2p_two_shot = int(value);
   else if (n == "p2p_debug") ctx->opt_p2p_debug = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);

@@ -211,7 +211,7 @@ int dba_comm_init(dba_ctx* ctx, int nranks, int rank, const void* id128);
 int dba_comm_destroy(dba_ctx* ctx);
 /* Optional, after dba_comm_init: replace the per-iteration ncclAllReduce by kernels over NVLink peer memory: ONE kernel
  * for reduced systems up to option "p2p_max_n" (default 1536), a reduce-scatter + all-gather pair above it (option
- * "p2p_two_shot", default 1), as long as (n + 1) * ld floats fit slab_bytes.  Every rank exports a buffer
+ * "p2p_two_shot": 1 = for two ranks, where it measured faster than NCCL (default), 2 = always, 0 = never), as long as (n + 1) * ld floats fit slab_bytes.  Every rank exports a buffer
  * (three regions of slab_bytes + flags; 64-byte cudaIpcMemHandle_t out), the handles are exchanged by the caller
  * (rank order) and imported.  One process per GPU, all GPUs of one box with peer access. */
 int dba_comm_p2p_export(dba_ctx* ctx, void* handle64_out, int64_t slab_bytes);
