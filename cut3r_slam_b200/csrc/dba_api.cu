@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <cstdio>
 #include <algorithm>
@@ -139,6 +140,13 @@ struct dba_ctx {
   P2PPeers p2p_peers{};
   bool p2p_ok = false;
   bool opt_p2p = true;
+  bool opt_nvtx = false;             // NVTX ranges around the call and its stages
+  bool opt_chi2 = false;             // objective before every iteration and after the last one (debug_read "chi2")
+  const int64_t* cur_ii_dev = nullptr;   // device edge lists of the call in flight (set by the entry points)
+  const int64_t* cur_jj_dev = nullptr;
+  DevBuf d_chi2;
+  int chi2_rows = 0;
+  int64_t chi2_E = 0;
   int opt_p2p_two_shot = 1;          // n > p2p_max_n: reduce-scatter + all-gather over peer memory instead of NCCL:
                                      // 0 never, 1 for two ranks (where it measured faster), 2 always
   int opt_p2p_max_n = 1536;          // larger systems are bandwidth-bound: NCCL's reduce-scatter + all-gather moves less
@@ -467,7 +475,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   // buffers, same scalars) is captured once and then replayed with ONE launch.  What this buys is launch latency:
   // the frontend / motion-only windows are 12-13 dependent kernels of 5-40 us per LM iteration.
   if (!capturing && ctx->opt_graphs && ii_h == nullptr && E > 0 && graph_key != 0 && cov_out == nullptr &&
-      iterations > 0 && !ctx->profile && !ctx->keep_system && !(ctx->comm != nullptr && ctx->nranks > 1)) {
+      iterations > 0 && !ctx->profile && !ctx->keep_system && !ctx->opt_chi2 && !(ctx->comm != nullptr && ctx->nranks > 1)) {
     const void* ptr[9] = {poses, disps, intr, disps_sens, targets, weights, eta, dx_out, dz_out};
     const int64_t dims[8] = {E, N, ht, wd, M, t0, t1, iterations};
     dba_ctx::BaGraph* hit = nullptr;
@@ -542,8 +550,37 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       ctx->ev.push_back(e);
     }
   }
-  auto mark = [&]() { if (prof) cudaEventRecord(ctx->ev[nev++], st); };
+  // option "nvtx": host-side ranges around the call and the stage launches (Nsight Systems timelines; no cost when off)
+  static const char* const kStage[6] = {"dba linearize", "dba assemble", "dba all-reduce", "dba cholesky+solve", "dba backsub", "dba retract"};
+  const bool nvtx = ctx->opt_nvtx;
+  int nvtx_stage = 0;
+  if (nvtx) nvtxRangePushA(capturing ? "dba_ba (capture)" : "dba_ba");
+  auto mark = [&]() {
+    if (prof) cudaEventRecord(ctx->ev[nev++], st);
+    if (nvtx) {
+      if (nvtx_stage > 0) nvtxRangePop();
+      if (nvtx_stage < 6) nvtxRangePushA(kStage[nvtx_stage]);
+      nvtx_stage = (nvtx_stage + 1) % 7;
+    }
+  };
+  struct NvtxCloser {          // every early return of the loop below leaves the ranges balanced
+    bool on; int* stage;
+    ~NvtxCloser() { if (on) { if (*stage > 0) nvtxRangePop(); nvtxRangePop(); } }
+  } nvtx_closer{nvtx, &nvtx_stage};
+  const bool chi2 = ctx->opt_chi2 && !capturing && cov_out == nullptr && g.E > 0 && ctx->cur_ii_dev != nullptr && iterations > 0;
+  if (chi2) {
+    CK(ctx->d_chi2.ensure(size_t(iterations + 1) * g.E * sizeof(double) + 16), "chi2 buffer");
+    ctx->chi2_rows = iterations + 1;
+    ctx->chi2_E = g.E;
+  } else if (!capturing) {
+    ctx->chi2_rows = 0;
+  }
+  auto chi2_at = [&](int row) {
+    return launch_chi2(poses, disps, intr, targets, weights, ctx->cur_ii_dev, ctx->cur_jj_dev, g.E, g.N, g.HW, g.wd,
+                       ctx->d_chi2.as<double>() + size_t(row) * g.E, st);
+  };
   for (int it = 0; it < iterations; ++it) {
+    if (chi2) CK(chi2_at(it), "chi2");
     mark();
     if (g.E > 0) {
       const bool fork = g.n_tc > 0 && (g.n_simt > 0 || g.n_wide > 0 || g.n_wide2 > 0) && ctx->side != nullptr;
@@ -658,6 +695,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     mark();
   }
   if (cov_out != nullptr) { ctx->last_launches = g_launch_count; return 0; }
+  if (chi2) CK(chi2_at(iterations), "chi2");
   if (prof && nev > 0) {
     CK(cudaEventSynchronize(ctx->ev[nev - 1]), "profile");
     for (int it = 0; it < iterations; ++it)
@@ -735,7 +773,7 @@ void dba_destroy(dba_ctx* c) {
   cudaSetDevice(c->device);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
   DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
-                    &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->s_poses, &c->s_disps, &c->s_intr,
+                    &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->d_chi2, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->d_pack, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
                     &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
                     &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep};
@@ -771,6 +809,8 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
   else if (n == "p2p_allreduce") ctx->opt_p2p = value != 0;
   else if (n == "p2p_max_n") ctx->opt_p2p_max_n = int(value);
   else if (n == "p2p_two_shot") ctx->opt_p2p_two_shot = int(value);
+  else if (n == "nvtx") ctx->opt_nvtx = value != 0;
+  else if (n == "chi2") ctx->opt_chi2 = value != 0;
   else if (n == "p2p_debug") ctx->opt_p2p_debug = int(value);
   else if (n == "cholesky_tc") ctx->opt_chol_tc = int(value);
   else if (n == "stream_inputs") g_tc_stream_mode = int(value);
@@ -820,8 +860,11 @@ int dba_ba_cached(dba_ctx* ctx, float* poses, float* disps, const float* intrins
       ih = ctx->h_idx; jh = ctx->h_idx + E;
     }
   }
-  return run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ih, jh, E, N, ht, wd, M, t0, t1,
-                iterations, lm, ep, motion_only != 0, dx_out, dz_out, st, nullptr, graph_key);
+  ctx->cur_ii_dev = ii; ctx->cur_jj_dev = jj;
+  rc = run_ba(ctx, poses, disps, intrinsics, disps_sens, targets, weights, eta, ih, jh, E, N, ht, wd, M, t0, t1,
+              iterations, lm, ep, motion_only != 0, dx_out, dz_out, st, nullptr, graph_key);
+  ctx->cur_ii_dev = nullptr; ctx->cur_jj_dev = nullptr;
+  return rc;
 }
 
 int dba_ba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
@@ -1310,6 +1353,19 @@ int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t c
     if (cap < int64_t(sizeof(d))) return -1;
     std::memcpy(host_out, d, sizeof(d));
     return sizeof(d);
+  }
+  if (n == "chi2") {               // double[iterations + 1] of the last call run with option "chi2": the objective before
+                                  // every iteration and after the last one (per-edge partial sums added here, edge order)
+    if (ctx->chi2_rows <= 0 || cap < int64_t(ctx->chi2_rows * sizeof(double))) return -1;
+    std::vector<double> h(size_t(ctx->chi2_rows) * ctx->chi2_E);
+    if (cudaMemcpy(h.data(), ctx->d_chi2.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    double* out = static_cast<double*>(host_out);
+    for (int r = 0; r < ctx->chi2_rows; ++r) {
+      double t = 0.0;
+      for (int64_t e = 0; e < ctx->chi2_E; ++e) t += h[size_t(r) * ctx->chi2_E + e];
+      out[r] = t;
+    }
+    return int64_t(ctx->chi2_rows * sizeof(double));
   }
   if (n == "graph_replays") {
     if (cap < int64_t(sizeof(int64_t))) return -1;

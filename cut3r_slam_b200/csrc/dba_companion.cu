@@ -194,6 +194,58 @@ k_depth_filter(const float* __restrict__ poses, const float* __restrict__ disps,
 
 }  // namespace
 
+// Objective of the reprojection problem at the current state (debug / convergence monitor, option "chi2"):
+//   chi2 = sum over edges and pixels of 0.001 * valid * (w_x r_x^2 + w_y r_y^2),  r = target - coords, the weighting of
+//   hislam2/geom/ba.py:44-45.  One CTA per edge, per-CTA partial sums in fp64 (deterministic slot per edge; the host
+//   adds the E slots).  Not on the optimisation path.
+namespace {
+__global__ void __launch_bounds__(256)
+k_chi2(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+       const float* __restrict__ targets, const float* __restrict__ weights, const int64_t* __restrict__ ii,
+       const int64_t* __restrict__ jj, int N, int HW, int wd, double* __restrict__ out) {
+  __shared__ float sRt[12];
+  __shared__ double sred[8];
+  const int e = blockIdx.x;
+  const int64_t i = ii[e], j = jj[e];
+  const bool ok = i >= 0 && i < N && j >= 0 && j < N;
+  if (threadIdx.x == 0 && ok) relative_pose_Rt(poses, int(i), int(j), sRt);
+  __syncthreads();
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  double acc = 0.0;
+  if (ok) {
+    float Rt[12];
+#pragma unroll
+    for (int t = 0; t < 12; ++t) Rt[t] = sRt[t];
+    const float* tg = targets + int64_t(e) * 2 * HW;
+    const float* wg = weights + int64_t(e) * 2 * HW;
+    for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+      const int py = p / wd, px = p - py * wd;
+      const Proj pr = project(Rt, (float(px) - cx) / fx, (float(py) - cy) / fy, disps[i * HW + p], fx, fy, cx, cy);
+      const float r0 = tg[p] - pr.u, r1 = tg[HW + p] - pr.v;
+      acc += double(kWeightScale * pr.valid * (wg[p] * r0 * r0 + wg[HW + p] * r1 * r1));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += sred[w];
+    out[e] = t;
+  }
+}
+}  // namespace
+
+cudaError_t launch_chi2(const float* poses, const float* disps, const float* intr, const float* targets,
+                        const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int N, int HW, int wd,
+                        double* out, cudaStream_t st) {
+  if (E <= 0) return cudaSuccess;
+  k_chi2<<<unsigned(E), 256, 0, st>>>(poses, disps, intr, targets, weights, ii, jj, N, HW, wd, out);
+  g_launch_count++;
+  return cudaGetLastError();
+}
+
 cudaError_t launch_frame_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                                   const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
                                   cudaStream_t st) {

@@ -104,6 +104,9 @@ cudaError_t launch_retract(const DeviceGraph& g, const BAInputs& in, const Works
 cudaError_t launch_frame_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                                   const int64_t* jj, int64_t K, int N, int ht, int wd, float beta, float* out,
                                   cudaStream_t st);
+cudaError_t launch_chi2(const float* poses, const float* disps, const float* intr, const float* targets,
+                        const float* weights, const int64_t* ii, const int64_t* jj, int64_t E, int N, int HW, int wd,
+                        double* out, cudaStream_t st);
 cudaError_t launch_covis_distance(const float* poses, const float* disps, const float* intr, const int64_t* ii,
                                   int64_t K, int N, int ht, int wd, float* out, cudaStream_t st);
 cudaError_t launch_iproj(const float* poses, const float* disps, const float* intr, int64_t K, int ht, int wd,

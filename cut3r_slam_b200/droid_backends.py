@@ -474,6 +474,18 @@ def graph_replays(device=None, _ctx=None):
     return int(buf[0])
 
 
+def chi2_history(device=None, _ctx=None):
+    """With option "chi2" on: the reprojection objective sum(0.001 valid w r^2) (the weighting of hislam2/geom/ba.py:44-45)
+    of the last `ba` call, before every LM iteration and after the last one -- a list of iterations + 1 floats.
+    A debug / convergence monitor (one extra kernel per iteration; the call graphs are off while it is on)."""
+    ctx = _ctx if _ctx is not None else context(device)
+    buf = (C.c_double * 256)()
+    n = ctx.lib.dba_debug_read(ctx.handle, b"chi2", buf, C.sizeof(buf))
+    if n < 0:
+        raise RuntimeError("no chi2 record: set_option('chi2', 1) before the ba call")
+    return [buf[i] for i in range(n // 8)]
+
+
 STAGES = ("linearize", "assemble", "allreduce", "cholesky", "backsub", "retract")
 
 

@@ -43,6 +43,9 @@ const char* dba_version(void);
  * "cuda_graphs" 0/1 -- dba_ba_cached calls that repeat an earlier call exactly (plan hit by graph_key, same buffer
  * addresses, sizes, iterations, lm, ep) are captured into a CUDA graph on their second occurrence and replayed with one
  * cudaGraphLaunch on `stream` afterwards (default 1; not under "profile" / "keep_system", not for sharded contexts);
+ * "chi2" 0/1 -- record the reprojection objective before every LM iteration and after the last one (one extra kernel per
+ * iteration; read with dba_debug_read "chi2"; default 0);
+ * "nvtx" 0/1 -- NVTX ranges around every call and its stages (host side, for Nsight Systems timelines; default 0);
  * "cluster_solve" 0/1 -- triangular solves as a panel chain through one thread-block cluster (n <= 768) or a
  * co-resident grid (larger n) instead of the single-CTA slab kernels (default 1; process-wide). */
 int dba_set_option(dba_ctx* ctx, const char* name, double value);
@@ -219,7 +222,7 @@ int dba_comm_p2p_import(dba_ctx* ctx, const void* handles /* [nranks][64] */, in
 
 /* ---- test / profiling hooks */
 /* name: "system" -> [(n6+1)*ld] floats of the last assembled reduced system (needs keep_system=1),
- * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; "graph_replays" -> int64 calls that ran as one
+ * "dims" -> int32[8] {n6, ld, Pp, M, S, ppl, degmax, npairs_max}; "chi2" -> double[iterations + 1] objective of the last call (option "chi2"); "graph_replays" -> int64 calls that ran as one
  * cudaGraphLaunch; "stage_ms" -> double[8] accumulated
  * {linearize, assemble, allreduce, cholesky+solve, backsub, retract, 0, LM iterations}; returns the number of BYTES
  * written (<= cap) or <0. Synchronous. */

@@ -435,3 +435,46 @@ def test_chain_triangular_solves_agree_with_slab_kernels(P, E, motion_only):
     assert float((chain[1] - slab[1]).abs().max()) < 1e-5
     assert rel_err(chain[2], slab[2]) < 1e-5
     assert torch.equal(chain[0], again[0]) and torch.equal(chain[1], again[1]) and torch.equal(chain[2], again[2])
+
+
+def test_nvtx_ranges_and_profile_option_leave_results_unchanged():
+    """Options "nvtx" (host-side NVTX ranges around the call and its stages) and "profile" (CUDA events per stage) are
+    observers: same bits with them on."""
+    db = _db()
+    p = make_problem("correctness")
+    a = p.to("cuda")
+    dx_a, _ = db.ba(*a.ba_args())
+    try:
+        db.set_option("nvtx", 1)
+        db.set_option("profile", 1)
+        b = p.to("cuda")
+        dx_b, _ = db.ba(*b.ba_args())
+        stages, n_it = db.stage_times()
+    finally:
+        db.set_option("nvtx", 0)
+        db.set_option("profile", 0)
+    assert torch.equal(dx_a, dx_b) and torch.equal(a.poses, b.poses) and torch.equal(a.disps, b.disps)
+    assert n_it == p.iterations and stages["linearize"] > 0 and stages["cholesky"] > 0
+
+
+@pytest.mark.parametrize("name", ["correctness", "frontend"])
+def test_chi2_monitor_matches_the_oracle_and_decreases(name):
+    """Option "chi2": the reprojection objective sum(0.001 valid w r^2) (hislam2/geom/ba.py:44-45 weighting) before every
+    iteration and after the last.  Its first value against the fp64 restatement of projective_transform
+    (hislam2/geom/projective_ops.py:44-74); the LM iterations of these problems reduce it monotonically."""
+    db = _db()
+    p = make_problem(name)
+    coords, valid = od.projective_transform(p.poses.double(), p.disps.double(), p.intrinsics.double(), p.ii, p.jj)
+    r = p.targets.double().permute(0, 2, 3, 1) - coords
+    ref0 = float((0.001 * valid * p.weights.double().permute(0, 2, 3, 1) * r * r).sum())
+    try:
+        db.set_option("chi2", 1)
+        g = p.to("cuda")
+        db.ba(*g.ba_args())
+        h = db.chi2_history()
+    finally:
+        db.set_option("chi2", 0)
+    assert len(h) == p.iterations + 1
+    assert abs(h[0] - ref0) <= 1e-4 * ref0, (h[0], ref0)
+    assert all(b < a for a, b in zip(h, h[1:])), h
+    assert h[-1] < 0.5 * h[0], h
