@@ -35,6 +35,7 @@
 #define DBA_V2_ABLATE 0
 #endif
 
+
 namespace dba {
 
 namespace {
@@ -264,10 +265,6 @@ k_linearize_v2(const LinParams P) {
     TR(1);
     // ---------------- phase 2 (warps 0-1, one pixel each): the edges' partials summed in a fixed order; the other
     // warps meanwhile add the PREVIOUS tile's tensor-core products into the shared-memory accumulator ------------
-    if (tile > tile_lo) {   // MMAs of the previous tile done: its accumulator readable, operand tiles reusable
-      mbar_wait(&mbar[(tile - tile_lo - 1) & 1], uint32_t((tile - tile_lo - 1) >> 1) & 1u);
-      tc_fence_after_sync();
-    }
 #ifdef DBA_V2_TRACE
     if (blockIdx.x == 0 && (tid == 0 || tid == 64)) { const long long t_ = clock64(); trw += t_ - tlast; tlast = t_; }
 #endif
@@ -331,6 +328,11 @@ k_linearize_v2(const LinParams P) {
       eta_c = eta_n;
       if (tile + 1 < tile_hi) fill_px(tile + 1, pl2, d_n);
     } else if (tile > tile_lo) {
+      // The wait for the previous tile's MMAs sits HERE, on the flush warps only: the reduce above needs neither the
+      // accumulator nor the operand tiles, so it runs while the tensor pipe finishes (the wait used to be in front of
+      // it, for all warps).  Warps 0-1 reach the operand tiles only behind the next barrier, i.e. after these waits.
+      mbar_wait(&mbar[(tile - tile_lo - 1) & 1], uint32_t((tile - tile_lo - 1) >> 1) & 1u);
+      tc_fence_after_sync();
       flush(((tile - tile_lo) & 1) ^ 1);
       tc_fence_before_sync();
     }
