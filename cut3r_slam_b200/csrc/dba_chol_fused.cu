@@ -221,12 +221,23 @@ __device__ __forceinline__ void diag_stage(CholSmem& S, float* A, float* Lm, flo
     {  // D -= X X^T : thread -> row r, columns c4..c4+3
       const int r = tid >> 3, c4 = (tid & 7) * 4;
       float4 d = *reinterpret_cast<const float4*>(&S.D[r][c4]);
-#pragma unroll 8
-      for (int m = 0; m < NB; ++m) {
-        const float xr = S.P[0][m][r];
-        const float4 xc = *reinterpret_cast<const float4*>(&S.P[0][m][c4]);
-        fms2(d.x, d.y, xr, xc.x, xc.y);
-        fms2(d.z, d.w, xr, xc.z, xc.w);
+      if (c4 <= r) {                       // only the lower triangle of the block is read afterwards
+        // four independent chains (m mod 4), added once at the end: the sum over m is what the factor needs, not its
+        // order (the panel solve that produced X is rounded already); 8 dependent FFMA2 per chain instead of 32
+        float4 e1 = make_float4(0.f, 0.f, 0.f, 0.f), e2 = e1, e3 = e1;
+#pragma unroll
+        for (int m = 0; m < NB; m += 4) {
+          const float x0 = S.P[0][m][r], x1 = S.P[0][m + 1][r], x2 = S.P[0][m + 2][r], x3 = S.P[0][m + 3][r];
+          const float4 c0 = *reinterpret_cast<const float4*>(&S.P[0][m][c4]);
+          const float4 c1 = *reinterpret_cast<const float4*>(&S.P[0][m + 1][c4]);
+          const float4 c2 = *reinterpret_cast<const float4*>(&S.P[0][m + 2][c4]);
+          const float4 c3 = *reinterpret_cast<const float4*>(&S.P[0][m + 3][c4]);
+          fms2(d.x, d.y, x0, c0.x, c0.y);   fms2(d.z, d.w, x0, c0.z, c0.w);
+          fms2(e1.x, e1.y, x1, c1.x, c1.y); fms2(e1.z, e1.w, x1, c1.z, c1.w);
+          fms2(e2.x, e2.y, x2, c2.x, c2.y); fms2(e2.z, e2.w, x2, c2.z, c2.w);
+          fms2(e3.x, e3.y, x3, c3.x, c3.y); fms2(e3.z, e3.w, x3, c3.z, c3.w);
+        }
+        d.x += (e1.x + e2.x) + e3.x; d.y += (e1.y + e2.y) + e3.y; d.z += (e1.z + e2.z) + e3.z; d.w += (e1.w + e2.w) + e3.w;
       }
       *reinterpret_cast<float4*>(&S.D[r][c4]) = d;
     }
@@ -606,10 +617,15 @@ k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx
     for (int e = tid; e < nrow * (n - r0); e += SMALL_T) {
       const int ri = e / (n - r0), rc = e - ri * (n - r0);
       if (rc <= ri) {
-        float acc = 0.f;
-#pragma unroll 8
-        for (int m = 0; m < NB; ++m) acc = fmaf(S.P[0][m][ri], S.P[0][m][rc], acc);
-        sA[(r0 + ri) * ld + r0 + rc] -= acc;
+        float acc = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;      // four chains: this single-CTA kernel is latency-bound
+#pragma unroll
+        for (int m = 0; m < NB; m += 4) {
+          acc = fmaf(S.P[0][m][ri], S.P[0][m][rc], acc);
+          acc1 = fmaf(S.P[0][m + 1][ri], S.P[0][m + 1][rc], acc1);
+          acc2 = fmaf(S.P[0][m + 2][ri], S.P[0][m + 2][rc], acc2);
+          acc3 = fmaf(S.P[0][m + 3][ri], S.P[0][m + 3][rc], acc3);
+        }
+        sA[(r0 + ri) * ld + r0 + rc] -= (acc + acc1) + (acc2 + acc3);
       }
     }
     __syncthreads();
@@ -627,9 +643,15 @@ k_chol_small(const float* __restrict__ A, int ldA, int n, float* __restrict__ dx
       xs[k0 + lane] = (lane < nb) ? t : 0.f;
       __syncwarp();
       const float* Li = sLi + kb * NB * NB;
-      float x = 0.f;
+      float x = 0.f, x1 = 0.f, x2 = 0.f, x3 = 0.f;
 #pragma unroll
-      for (int r = 0; r < NB; ++r) x = fmaf(Li[r * NB + lane], xs[k0 + r], x);
+      for (int r = 0; r < NB; r += 4) {
+        x = fmaf(Li[r * NB + lane], xs[k0 + r], x);
+        x1 = fmaf(Li[(r + 1) * NB + lane], xs[k0 + r + 1], x1);
+        x2 = fmaf(Li[(r + 2) * NB + lane], xs[k0 + r + 2], x2);
+        x3 = fmaf(Li[(r + 3) * NB + lane], xs[k0 + r + 3], x3);
+      }
+      x = (x + x1) + (x2 + x3);
       __syncwarp();
       if (lane < nb) xs[k0 + lane] = x;
       __syncwarp();
