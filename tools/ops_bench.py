@@ -101,6 +101,25 @@ def main():
     # depth covariance: one linearisation + factorisation + S^-1 + per-pixel quadratic forms
     row("depth_cov", timeit(lambda: db.depth_cov(g.poses, g.disps, g.intrinsics, None, g.targets, g.weights, g.eta, g.ii, g.jj,
                                                  p.t0, p.t1, p.lm, p.ep), a.reps, flush), None, n=6 * (p.t1 - p.t0))
+    # pgba: Sim3 pose-graph BA on the same graph (scales 1, 16 relative-pose factors), 2 iterations per call
+    poses8 = torch.cat([g.poses, torch.ones(N, 1, device="cuda")], 1).contiguous()
+    R = 16
+    rel_ii = torch.arange(2, 2 + R, device="cuda")
+    rel_jj = rel_ii + 5
+    rel_poses = torch.zeros(R, 7, device="cuda"); rel_poses[:, 6] = 1.0
+    rel_infos = torch.eye(7, device="cuda").expand(R, 7, 7).contiguous()
+    d1 = g.disps.clone()
+
+    def pg():
+        db.pgba(poses8, d1, g.intrinsics, g.targets, g.weights, g.eta, g.ii, g.jj, rel_ii, rel_jj, rel_poses, rel_infos,
+                p.t0, p.t1, 2, p.lm, p.ep, 1e-5)
+    row("pgba_2it", timeit(pg, max(3, a.reps // 4), flush), None, n=7 * (p.t1 - p.t0), rel_factors=R)
+    # the other elementwise steps of FactorGraph.update
+    tgt = g.targets.permute(0, 2, 3, 1).contiguous()[None]
+    row("motion_features", timeit(lambda: glue.motion_features(g.poses, g.disps, g.intrinsics, g.ii, g.jj, tgt), a.reps, flush), E * HW * (4 + 8 + 12 + 16))
+    damping = torch.rand_like(g.disps) * 1e-3
+    row("damping_eta", timeit(lambda: glue.damping_eta(damping, g.ii), a.reps, flush), M * HW * 8)
+    row("covis_distance", timeit(lambda: db.covis_distance(g.poses, g.disps, g.intrinsics, torch.arange(N - 1, device="cuda")), a.reps, flush), None, pairs=N - 1)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(rows, open(os.path.join(ROOT, "gpurun_out", f"ops_bench_{a.workload}.json"), "w"), indent=1)
 
