@@ -933,6 +933,7 @@ int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, 
   a.rel_ii = rel_ii; a.rel_jj = rel_jj; a.rel_poses = rel_poses; a.rel_infos = rel_infos; a.pw = pw; a.lm = lm; a.ep = ep;
   a.E = int(E); a.N = int(N); a.M = P.M; a.R = int(R); a.HW = int(HW); a.wd = wd; a.t0 = t0; a.Pp = Pp; a.nSblk = P.nSblk;
   a.npairs_max = P.npairs_max; a.ldA = ld;
+  a.nblkmax = P.nblkmax;
   a.Hblk = ctx->pg_H.as<float>(); a.vblk = ctx->pg_v.as<float>(); a.Ep = ctx->pg_Ep.as<float>(); a.CW = ctx->pg_CW.as<float>();
   a.Q = ctx->pg_Q.as<float>(); a.Wv = ctx->pg_W.as<float>(); a.Eis = ctx->pg_Eis.as<float>(); a.Spart = ctx->pg_S.as<float>();
   a.vEpart = ctx->pg_vE.as<float>(); a.Hsp = ctx->pg_Hsp.as<float>(); a.vsp = ctx->pg_vsp.as<float>(); a.A = ctx->pg_A.as<float>();

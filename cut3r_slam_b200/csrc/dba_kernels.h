@@ -135,6 +135,7 @@ struct PgbaArgs {
   const float *rel_poses, *rel_infos;  // [R,7], [R,7,7]
   float pw, lm, ep;
   int E, N, M, R, HW, wd, t0, Pp, nSblk, npairs_max, ldA;
+  int nblkmax = 0;           // largest number of panel blocks of a keyframe (out-degree + 1)
   float *Hblk, *vblk, *Ep, *CW, *Q, *Wv, *Eis, *Spart, *vEpart, *Hsp, *vsp, *A, *dx, *dz;
 };
 cudaError_t launch_pgba_linearize(const PgbaArgs& a, cudaStream_t st);

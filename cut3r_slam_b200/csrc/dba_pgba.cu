@@ -340,6 +340,78 @@ k_pg_schur(const float* __restrict__ Ep, const float* __restrict__ Eis, const fl
   }
 }
 
+// The same products with one CTA per (keyframe, panel block A): the seven rows of E_A are staged once in shared memory
+// (7 HW floats, 93 KB at 43 x 77: two CTAs per SM) and the CTA walks B = 0 .. A, so only the E_B rows stream from L2 --
+// half the traffic of the pair-per-CTA kernel (3.5 GB per iteration on the backend graph, the L2 bound of pgba).
+// Each thread still adds its pixels in ascending order: bit-identical slabs.  Largest A first.
+__global__ void __launch_bounds__(PG_T)
+k_pg_schur_rows(const float* __restrict__ Ep, const float* __restrict__ Eis, const float* __restrict__ Q,
+                const float* __restrict__ Wv, const int32_t* __restrict__ koff, const int32_t* __restrict__ pairbase,
+                const int32_t* __restrict__ blkbase, int HW, int nblkmax, float* __restrict__ Spart,
+                float* __restrict__ vEpart) {
+  extern __shared__ __align__(16) float sEa[];              // [7][HW]
+  __shared__ float sred[PG_T / 32][56];
+  const int m = blockIdx.y, A = nblkmax - 1 - int(blockIdx.x);
+  const int e0 = koff[m], nblk = koff[m + 1] - e0 + 1;
+  if (A >= nblk) return;
+  const float* ea = (A == 0) ? Eis + int64_t(m) * 7 * HW : Ep + (int64_t(e0 + A - 1) * 14 + 7) * HW;
+  const float* q = Q + int64_t(m) * HW;
+  const float* wv = Wv + int64_t(m) * HW;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < 7 * HW; i += PG_T) sEa[i] = ea[i];
+  __syncthreads();
+  for (int B = 0; B <= A; ++B) {
+    const float* eb = (B == 0) ? Eis + int64_t(m) * 7 * HW : Ep + (int64_t(e0 + B - 1) * 14 + 7) * HW;
+    float acc[56];
+#pragma unroll
+    for (int k = 0; k < 56; ++k) acc[k] = 0.f;
+    // two pixels per pass: sixteen L2 loads in flight per thread (two CTAs per SM leave only 16 warps to hide them)
+    for (int p = tid; p < HW; p += 2 * PG_T) {
+      const int p1 = p + PG_T;
+      const bool two = p1 < HW;
+      float b[7], b1[7];
+#pragma unroll
+      for (int k = 0; k < 7; ++k) { b[k] = eb[int64_t(k) * HW + p]; b1[k] = two ? eb[int64_t(k) * HW + p1] : 0.f; }
+      const float qq = q[p], qw = qq * wv[p];
+      const float qq1 = two ? q[p1] : 0.f, qw1 = two ? qq1 * wv[p1] : 0.f;
+#pragma unroll
+      for (int r = 0; r < 7; ++r) {
+        const float ar = sEa[r * HW + p];
+        const float qa = qq * ar;
+#pragma unroll
+        for (int c = 0; c < 7; ++c) acc[r * 7 + c] += qa * b[c];
+        acc[49 + r] += qw * ar;
+      }
+      if (two) {
+#pragma unroll
+        for (int r = 0; r < 7; ++r) {
+          const float ar = sEa[r * HW + p1];
+          const float qa = qq1 * ar;
+#pragma unroll
+          for (int c = 0; c < 7; ++c) acc[r * 7 + c] += qa * b1[c];
+          acc[49 + r] += qw1 * ar;
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 56; ++k) {
+      float v = acc[k];
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) sred[warp][k] = v;
+    }
+    __syncthreads();
+    if (tid < 56) {
+      float v = 0.f;
+      for (int w = 0; w < PG_T / 32; ++w) v += sred[w][tid];
+      const int pi = A * (A + 1) / 2 + B;
+      if (tid < 49) Spart[(int64_t(pairbase[m]) + pi) * 49 + tid] = v;
+      else if (A == B) vEpart[(int64_t(blkbase[m]) + A) * 7 + (tid - 49)] = v;
+    }
+    __syncthreads();
+  }
+}
+
 // reduced system: block ob of the lower block triangle (CTAs [0, nSblk)) or the rhs of pose a (CTAs nSblk ..),
 // gathered in the plan's fixed order with fp64 sums; chol.py:55-57 damping on the true diagonal
 __global__ void __launch_bounds__(64)
@@ -533,8 +605,16 @@ cudaError_t launch_pgba_linearize(const PgbaArgs& a, cudaStream_t st) {
   k_pg_edge<<<a.E, PG_T, 0, st>>>(a.poses, a.disps, a.intr, a.targets, a.weights, a.ci, a.cj, a.cedge, HW, a.wd, a.Hblk,
                                   a.vblk, a.Ep, a.CW);
   k_pg_cq<<<dim3((HW + 255) / 256, a.M), 256, 0, st>>>(a.CW, a.Ep, a.eta, a.koff, HW, a.Q, a.Wv, a.Eis);
-  k_pg_schur<<<dim3(a.npairs_max, a.M), PG_T, 0, st>>>(a.Ep, a.Eis, a.Q, a.Wv, a.koff, a.pairbase, a.blkbase, HW, a.Spart,
-                                                       a.vEpart);
+  const size_t smem_rows = size_t(7) * HW * sizeof(float);
+  if (a.nblkmax > 0 && smem_rows <= size_t(100) * 1024) {     // two CTAs per SM; larger images keep the pair-per-CTA kernel
+    cudaError_t e = cudaFuncSetAttribute(k_pg_schur_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_rows));
+    if (e != cudaSuccess) return e;
+    k_pg_schur_rows<<<dim3(a.nblkmax, a.M), PG_T, smem_rows, st>>>(a.Ep, a.Eis, a.Q, a.Wv, a.koff, a.pairbase, a.blkbase, HW,
+                                                                   a.nblkmax, a.Spart, a.vEpart);
+  } else {
+    k_pg_schur<<<dim3(a.npairs_max, a.M), PG_T, 0, st>>>(a.Ep, a.Eis, a.Q, a.Wv, a.koff, a.pairbase, a.blkbase, HW, a.Spart,
+                                                         a.vEpart);
+  }
   k_pg_assemble<<<a.nSblk + a.Pp, 64, 0, st>>>(a.sblk_off, a.sblk_items, a.rhs_off, a.rhs_items, a.Hblk, a.vblk, a.Spart,
                                                a.vEpart, a.nSblk, a.Pp, a.lm, a.ep, a.A, a.ldA);
   g_launch_count += 4;
