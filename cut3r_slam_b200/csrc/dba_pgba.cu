@@ -192,9 +192,14 @@ k_pg_edge(const float* __restrict__ poses, const float* __restrict__ disps, cons
   const float* tg = targets + int64_t(cedge[c]) * 2 * HW;
   const float* wg = weights + int64_t(cedge[c]) * 2 * HW;
   const float* dsrc = disps + int64_t(i) * HW;
-  float acc[NG];
+  // Reduced form (the one the 6-dof kernels use, tests/test_kernel_algebra.py): Ji = -Jj Ad is never formed.  Per pixel
+  // only the 7 x 7 Gram of Jj, vj and Ej are accumulated (35 sums instead of 119, 133 flops instead of 364); the
+  // source-pose row is Ei = -Ad^T Ej, and the blocks follow once per edge: Hji = -Hjj Ad, Hij = Hji^T,
+  // Hii = Ad^T Hjj Ad = -Ad^T Hji, vi = -Ad^T vj.
+  constexpr int NR = 28 + 7;
+  float acc[NR];
 #pragma unroll
-  for (int k = 0; k < NG; ++k) acc[k] = 0.f;
+  for (int k = 0; k < NR; ++k) acc[k] = 0.f;
   for (int p = tid; p < HW; p += PG_T) {
     const int py = p / wd, px = p - py * wd;
     const float dd = dsrc[p];
@@ -203,65 +208,89 @@ k_pg_edge(const float* __restrict__ poses, const float* __restrict__ disps, cons
     const float rr[2] = {tg[p] - pr.u, tg[HW + p] - pr.v};
     const float ww[2] = {kWeightScale * (pr.valid * wg[p]), kWeightScale * (pr.valid * wg[HW + p])};
     const float jz[2] = {pr.jz0, pr.jz1};
-    float J[2][14];
+    float J[2][7];
     // Jj = Jp Ja: [d g, X1 x g, X1 . g]  with g0 = [a0, 0, c0], g1 = [0, b1, c1]
-    J[0][7] = dd * pr.a0; J[0][8] = 0.f; J[0][9] = dd * pr.c0;
-    J[0][10] = Y * pr.c0; J[0][11] = Z * pr.a0 - X * pr.c0; J[0][12] = -Y * pr.a0; J[0][13] = pr.a0 * X + pr.c0 * Z;
-    J[1][7] = 0.f; J[1][8] = dd * pr.b1; J[1][9] = dd * pr.c1;
-    J[1][10] = Y * pr.c1 - Z * pr.b1; J[1][11] = -X * pr.c1; J[1][12] = X * pr.b1; J[1][13] = pr.b1 * Y + pr.c1 * Z;
-    float e14[14], ck = 0.f, wk = 0.f;
+    J[0][0] = dd * pr.a0; J[0][1] = 0.f; J[0][2] = dd * pr.c0;
+    J[0][3] = Y * pr.c0; J[0][4] = Z * pr.a0 - X * pr.c0; J[0][5] = -Y * pr.a0; J[0][6] = pr.a0 * X + pr.c0 * Z;
+    J[1][0] = 0.f; J[1][1] = dd * pr.b1; J[1][2] = dd * pr.c1;
+    J[1][3] = Y * pr.c1 - Z * pr.b1; J[1][4] = -X * pr.c1; J[1][5] = X * pr.b1; J[1][6] = pr.b1 * Y + pr.c1 * Z;
+    float ej[7], ck = 0.f, wk = 0.f;
 #pragma unroll
-    for (int k = 0; k < 14; ++k) e14[k] = 0.f;
+    for (int k = 0; k < 7; ++k) ej[k] = 0.f;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-#pragma unroll
-      for (int cc = 0; cc < 7; ++cc) {                           // Ji = -(Jj Ad)  (projective_ops.py:66-67)
-        float a = 0.f;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) a += J[r][7 + k] * sAd[k * 7 + cc];
-        J[r][cc] = -a;
-      }
       const float w = ww[r];
       int q = 0;
 #pragma unroll
-      for (int a = 0; a < 14; ++a) {
+      for (int a = 0; a < 7; ++a) {
         const float wa = w * J[r][a];
 #pragma unroll
-        for (int b = 0; b <= a; ++b) acc[q++] += wa * J[r][b];
-        acc[105 + a] += wa * rr[r];
-        e14[a] += wa * jz[r];
+        for (int bb = 0; bb <= a; ++bb) acc[q++] += wa * J[r][bb];
+        acc[28 + a] += wa * rr[r];
+        ej[a] += wa * jz[r];
       }
       ck += w * jz[r] * jz[r];
       wk += w * rr[r] * jz[r];
     }
 #pragma unroll
-    for (int k = 0; k < 14; ++k) Ep[(int64_t(c) * 14 + k) * HW + p] = e14[k];
+    for (int cc = 0; cc < 7; ++cc) {                             // Ei = -Ad^T Ej
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k < 7; ++k) a += ej[k] * sAd[k * 7 + cc];
+      Ep[(int64_t(c) * 14 + cc) * HW + p] = -a;
+    }
+#pragma unroll
+    for (int k = 0; k < 7; ++k) Ep[(int64_t(c) * 14 + 7 + k) * HW + p] = ej[k];
     CW[(int64_t(c) * 2) * HW + p] = ck;
     CW[(int64_t(c) * 2 + 1) * HW + p] = wk;
   }
 #pragma unroll
-  for (int k = 0; k < NG; ++k) {
+  for (int k = 0; k < NR; ++k) {
     float v = acc[k];
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) sred[warp][k] = v;
   }
   __syncthreads();
-  if (tid < NG) {
+  __shared__ float sHjj[49], sHji[49], svj[7];
+  if (tid < NR) {
     float v = 0.f;
     for (int w = 0; w < PG_T / 32; ++w) v += sred[w][tid];
-    if (tid < 105) {
+    if (tid < 28) {
       int a = 0;
       while ((a + 1) * (a + 2) / 2 <= tid) ++a;
-      const int b = tid - a * (a + 1) / 2;                        // a >= b in the 14 x 14 Gram
-      float* out = Hblk + int64_t(c) * 4 * 49;
-      if (a < 7) { out[0 * 49 + a * 7 + b] = v; out[0 * 49 + b * 7 + a] = v; }                    // Hii
-      else if (b >= 7) { out[3 * 49 + (a - 7) * 7 + (b - 7)] = v; out[3 * 49 + (b - 7) * 7 + (a - 7)] = v; }   // Hjj
-      else { out[2 * 49 + (a - 7) * 7 + b] = v; out[1 * 49 + b * 7 + (a - 7)] = v; }              // Hji, Hij = Hji^T
+      const int bb = tid - a * (a + 1) / 2;
+      sHjj[a * 7 + bb] = v; sHjj[bb * 7 + a] = v;
     } else {
-      const int a = tid - 105;
-      vblk[int64_t(c) * 14 + a] = v;                              // vi (0-6), vj (7-13)
+      svj[tid - 28] = v;
     }
+  }
+  __syncthreads();
+  float* out = Hblk + int64_t(c) * 4 * 49;
+  if (tid < 49) {                                                // Hji = -Hjj Ad
+    const int r = tid / 7, cc = tid - r * 7;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a += sHjj[r * 7 + k] * sAd[k * 7 + cc];
+    sHji[tid] = -a;
+    out[2 * 49 + tid] = -a;                                      // Hji
+    out[1 * 49 + cc * 7 + r] = -a;                               // Hij = Hji^T
+    out[3 * 49 + tid] = sHjj[tid];                               // Hjj
+  } else if (tid < 56) {                                         // vi = -Ad^T vj
+    const int cc = tid - 49;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a += sAd[k * 7 + cc] * svj[k];
+    vblk[int64_t(c) * 14 + cc] = -a;
+    vblk[int64_t(c) * 14 + 7 + cc] = svj[cc];
+  }
+  __syncthreads();
+  if (tid < 49) {                                                // Hii = -Ad^T Hji
+    const int r = tid / 7, cc = tid - r * 7;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a += sAd[k * 7 + r] * sHji[k * 7 + cc];
+    out[0 * 49 + tid] = -a;
   }
 }
 
