@@ -128,7 +128,7 @@ struct dba_ctx {
   // dba_pgba (Sim3): its own plan (S = 1) and workspace
   Plan pg_plan;
   DevBuf pg_i32, pg_items, pg_H, pg_v, pg_Ep, pg_CW, pg_Q, pg_W, pg_Eis, pg_S, pg_vE, pg_Hsp, pg_vsp, pg_A, pg_Lm, pg_Ldiag,
-      pg_dx, pg_dz, pg_fail, pg_keep;
+      pg_dx, pg_dz, pg_fail, pg_keep, pg_smsg, pg_sflag;
   int pt_M = 0, pt_N = 0;
   bool pt_contig = true;       // unique(ii) is a contiguous range of frames
   // NCCL
@@ -776,7 +776,7 @@ void dba_destroy(dba_ctx* c) {
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->d_chi2, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->d_pack, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
                     &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
-                    &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep};
+                    &c->pg_Ldiag, &c->pg_dx, &c->pg_dz, &c->pg_fail, &c->pg_keep, &c->pg_smsg, &c->pg_sflag};
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   for (auto& ge : c->graphs) if (ge.exec) cudaGraphExecDestroy(ge.exec);
@@ -941,6 +941,11 @@ int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, 
   Workspace ws{};
   ws.A = a.A; ws.ldA = ld; ws.Lm = ctx->pg_Lm.as<float>(); ws.Ldiag = ctx->pg_Ldiag.as<float>(); ws.dx = a.dx;
   ws.fail = ctx->pg_fail.as<int>();
+  if (trisolve_grid_msg_floats(n7) > 0) {            // n > 768: message slots of the grid-chain triangular solves
+    CK(ctx->pg_smsg.ensure(trisolve_grid_msg_floats(n7) * f), "pgba workspace");
+    CK(ctx->pg_sflag.ensure(trisolve_grid_flag_words(n7) * sizeof(unsigned), true), "pgba workspace");
+    ws.solve_msg = ctx->pg_smsg.as<float>(); ws.solve_flag = ctx->pg_sflag.as<unsigned>();
+  }
   const int coop = cholesky_coop_max_ctas(n7);
   g_launch_count = 0;
   for (int it = 0; it < iterations; ++it) {
