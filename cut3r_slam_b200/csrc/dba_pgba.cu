@@ -566,7 +566,8 @@ k_pg_rel_scatter(const float* __restrict__ Hsp, const float* __restrict__ vsp, c
       if (ia) Amat[int64_t(7 * Pp) * ld + 7 * a + k] += vsp[(int64_t(0) * R + f) * 7 + k];
       if (ib) Amat[int64_t(7 * Pp) * ld + 7 * b + k] += vsp[(int64_t(1) * R + f) * 7 + k];
     }
-    __syncthreads();
+    // no barrier between factors: thread t owns entry (r, c) of EVERY block it touches, so two factors that meet in
+    // one block are added by the same thread, in factor order
   }
 }
 
