@@ -657,13 +657,17 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
         return 1000 + r;
       }
     }
-    // iterative refinement (dba_refine.cu) of the cooperative solve on the LAST iteration of the call: an earlier
-    // iteration's solver error (4e-4 of dx at n = 756, 6e-3 at n = 3060) is corrected by the next relinearisation,
-    // the last one's would stay in the result.  "refine" = 2: every iteration (costs two more triangular solves:
-    // +65 us at n = 756, +1 ms at n = 3060 with the single-CTA solves)
+    // iterative refinement (dba_refine.cu) of the cooperative solve on the LAST TWO iterations of the call: an earlier
+    // iteration's solver error (4e-4 of dx at n = 756, 6e-3 at n = 3060) is corrected by the relinearisations that
+    // follow, the last one's would stay in the result -- and so does most of the one before it along weakly observed
+    // directions, where one more iteration contracts little (a chain-end keyframe on a 2-iteration call: disps 3.7e-4
+    // from the fp64 result against 2.5e-5 with both iterations refined, the reference's own fp32 run 7.7e-5;
+    // profiles/r2_parity_margins.md; motion-only calls have no disparity update to amplify it and keep refining the
+    // last iteration only).  "refine" = 2: every iteration (+39 us each at n = 756: the copy of the system, the fp64
+    // residual, two chain solves)
     const bool coop_path = cov_out == nullptr && !(ctx->opt_small && g.n6 <= cholesky_small_max_n()) &&
                            ctx->coop_ctas > 0 && !ctx->opt_multilaunch_chol;
-    const bool refine = coop_path && ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it == iterations - 1);
+    const bool refine = coop_path && ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it >= iterations - (motion_only ? 1 : 2));
     if (ctx->keep_system || refine)
       CK(cudaMemcpyAsync(ctx->Akeep.p, ws.A, size_t(g.n6 + 1) * ws.ldA * sizeof(float), cudaMemcpyDeviceToDevice, st),
          "keep_system");

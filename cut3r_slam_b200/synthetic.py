@@ -124,8 +124,9 @@ def make_edges(P, E, r, gen):
 
 def make_problem(name=None, *, P=None, E=None, ht=None, wd=None, iters=2, lm=1e-4, ep=0.1, t0=2, r=3,
                  motion_only=False, seed=1234, pose_noise=0.02, disp_noise=0.1, flow_noise=0.1,
-                 device="cpu"):
-    """Build a seeded problem. `name` picks one of CONFIGS; keyword overrides apply on top."""
+                 device="cpu", edges=None):
+    """Build a seeded problem. `name` picks one of CONFIGS; keyword overrides apply on top.
+    `edges=(ii, jj)` replaces the generated edge list (ragged / degenerate graphs of the parity tests)."""
     if name is not None:
         c = dict(CONFIGS[name])
         P, E, ht, wd = P or c["P"], E or c["E"], ht or c["ht"], wd or c["wd"]
@@ -144,7 +145,11 @@ def make_problem(name=None, *, P=None, E=None, ht=None, wd=None, iters=2, lm=1e-
     depth = torch.nn.functional.avg_pool2d(torch.nn.functional.pad(depth, (2, 2, 2, 2), mode="replicate"), 5, 1)[:, 0]
     gt_disps = 1.0 / depth
     intr = torch.tensor([0.8 * wd, 0.8 * wd, wd / 2.0, ht / 2.0], dtype=f64)
-    ii, jj = make_edges(P, E, r, gen)
+    if edges is None:
+        ii, jj = make_edges(P, E, r, gen)
+    else:
+        ii, jj = (torch.as_tensor(e, dtype=torch.long).reshape(-1) for e in edges)
+        E = int(ii.numel())
     targets = _reproject(Rg, tg, gt_disps, intr, ii, jj) + flow_noise * torch.randn(E, 2, ht, wd, generator=gen, dtype=f64)
     weights = torch.rand(E, 2, ht, wd, generator=gen, dtype=f64)
     M = int(torch.unique(ii).numel())

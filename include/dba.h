@@ -36,8 +36,8 @@ const char* dba_version(void);
  * "profile" 0/1 -- bracket every stage with CUDA events on `stream` and accumulate per-stage times
  * (setting it resets the accumulators; the call then waits for its last event before returning);
  * "tensor_cores" 0/1 -- Schur products on tcgen05 (default 1); "linearize_v2" 0/1 -- the one-warp-per-edge kernel for
- * out-degree <= 20 (default 1); "refine" 0/1/2 -- iterative refinement of the pose solve: off / last iteration of a call /
- * every iteration (default 1); "cholesky_tc" n -- 128-column-panel factorisation with tcgen05 trailing update from system
+ * out-degree <= 20 (default 1); "refine" 0/1/2 -- iterative refinement of the pose solve: off / last two iterations of a
+ * call (motion-only: the last one) / every iteration (default 1); "cholesky_tc" n -- 128-column-panel factorisation with tcgen05 trailing update from system
  * size n on (default 0 = off); "p2p_allreduce" 0/1, "p2p_max_n"; "stream_inputs" -1/0/1; "wide_tensor_cores" 0/1/2 -- keyframes with
  * out-degree 21..25 (1) and 26..41 (2) on the WIDE tcgen05 variants instead of the SIMT kernel (default 2);
  * "cuda_graphs" 0/1 -- dba_ba_cached calls that repeat an earlier call exactly (plan hit by graph_key, same buffer
