@@ -101,6 +101,17 @@ struct dba_ctx {
   uint64_t plan_key = 0;             // caller's identity of the edge lists the plan was built from (0: none)
   DevBuf d_plan_i32, d_items;
   DeviceGraph g{};
+  // second plan slot: dba_depth_cov linearises on the fp32 SIMT kernels (see there) and keeps its plan here, so that
+  // ba and depth_cov calls alternating on one graph rebuild neither plan (swap_plan_slot)
+  struct PlanSlot {
+    Plan plan;
+    bool valid = false, v2 = false;
+    int ppl = 0, tps = 1, HW = 0, ht = 0, wd = 0;
+    uint64_t key = 0;
+    DevBuf i32, items;
+    DeviceGraph g{};
+  } cov_slot;
+  int32_t last_dims[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // of the plan the last call ran on (debug_read "dims")
   // workspace
   DevBuf Hpart, Spart, vEpart, Q, w, Hblk, vblk, A, Lm, Ldiag, dx, dz, fail, Akeep, solve_msg, solve_flag;
   int coop_ctas = -1, coop_n = -1;   // cooperative Cholesky: co-resident CTA budget for the cached n6
@@ -186,6 +197,14 @@ int fail_cuda(dba_ctx* c, cudaError_t e, const char* where) {
     cudaError_t e__ = (call);                                \
     if (e__ != cudaSuccess) return fail_cuda(ctx, e__, where); \
   } while (0)
+
+void swap_plan_slot(dba_ctx* c) {
+  auto& a = c->cov_slot;
+  std::swap(c->plan, a.plan); std::swap(c->plan_valid, a.valid); std::swap(c->plan_v2, a.v2);
+  std::swap(c->plan_ppl, a.ppl); std::swap(c->plan_tps, a.tps); std::swap(c->plan_HW, a.HW);
+  std::swap(c->plan_ht, a.ht); std::swap(c->plan_wd, a.wd); std::swap(c->plan_key, a.key);
+  std::swap(c->d_plan_i32, a.i32); std::swap(c->d_items, a.items); std::swap(c->g, a.g);
+}
 
 int out_degree_max(const int64_t* ii, int64_t E, int N, int* M_out) {
   std::vector<int> deg(N, 0);
@@ -467,6 +486,11 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
     rc = prepare_plan(ctx, ii_h, jj_h, E, int(N), ht, wd, motion_only ? -1 : M, t0, t1, motion_only, st);
     if (rc) return rc;
     ctx->plan_key = graph_key;
+  }
+  {
+    const int32_t d[8] = {ctx->plan.n6, (ctx->plan.n6 + 1 + 3) & ~3, ctx->plan.Pp, ctx->plan.M, ctx->plan.S, ctx->plan_ppl,
+                          ctx->plan.degmax, ctx->plan.npairs_max};
+    std::memcpy(ctx->last_dims, d, sizeof(d));
   }
   Workspace ws{};
   rc = ensure_workspace(ctx, ws);
@@ -776,7 +800,7 @@ void dba_destroy(dba_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-  DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
+  DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->cov_slot.i32, &c->cov_slot.items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->d_chi2, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->d_pack, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
                     &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
@@ -825,6 +849,7 @@ int dba_set_option(dba_ctx* ctx, const char* name, double value) {
     if (!(v == 0 || v == 1 || v == 2 || v == 4 || v == 8)) return fail_arg(ctx, "ppl must be 0,1,2,4,8");
     ctx->opt_ppl = v; ctx->plan_valid = false;
   } else return fail_arg(ctx, "unknown option " + n);
+  ctx->cov_slot.valid = false;
   return 0;
 }
 
@@ -957,7 +982,7 @@ int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, 
     if (n7 <= cholesky_small_max_n()) {
       CK(launch_cholesky_small(ws, n7, st), "cholesky (single CTA)");
     } else if (coop > 0) {
-      const bool refine = ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it == iterations - 1);
+      const bool refine = ctx->opt_refine != 0 && (ctx->opt_refine >= 2 || it >= iterations - 2);   // as in run_ba
       if (refine) CK(cudaMemcpyAsync(ctx->pg_keep.p, a.A, size_t(n7 + 1) * ld * f, cudaMemcpyDeviceToDevice, st), "pgba keep");
       CK(launch_cholesky_coop(ws, n7, coop, st, !refine), "cholesky (cooperative)");
       if (refine) CK(launch_refine(ws, ctx->pg_keep.as<float>(), n7, st), "refinement");
@@ -985,9 +1010,21 @@ int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const fl
   CK(cudaSetDevice(ctx->device), "cudaSetDevice");
   rc = fetch_edge_lists(ctx, ii, jj, E, st);
   if (rc) return rc;
+  // The covariance linearises on the plain fp32 kernels.  The TMEM accumulation of the tcgen05 Schur products
+  // truncates: eight adds per flush shrink every entry of E Q E^T by ~2e-7, COHERENTLY -- harmless for dx (within the
+  // reference's own fp32 noise), but u^T S^-1 u amplifies a coherent relative error of E Q E^T ~700x on ill-conditioned
+  // graphs where random rounding of the same size is amplified ~100x (tools/cov_diag.py, profiles/r2_parity_margins.md:
+  // 1.4e-4 .. 2.3e-4 per pixel against 3e-5 .. 4e-5 for the reference's fp32 run; 7e-5 on the fp32 kernels).
+  // Its plan has its own slot, so the ba plan of the same graph survives.
   // the state is read-only on this path (run_ba's cov branch leaves before any retraction)
-  return run_ba(ctx, const_cast<float*>(poses), const_cast<float*>(disps), intrinsics, disps_sens, targets, weights, eta,
-                ctx->h_idx, ctx->h_idx + E, E, N, ht, wd, M, t0, t1, 1, lm, ep, false, nullptr, nullptr, st, dzcov_out);
+  const bool tc = ctx->opt_tc;
+  swap_plan_slot(ctx);
+  ctx->opt_tc = false;
+  rc = run_ba(ctx, const_cast<float*>(poses), const_cast<float*>(disps), intrinsics, disps_sens, targets, weights, eta,
+              ctx->h_idx, ctx->h_idx + E, E, N, ht, wd, M, t0, t1, 1, lm, ep, false, nullptr, nullptr, st, dzcov_out);
+  ctx->opt_tc = tc;
+  swap_plan_slot(ctx);
+  return rc;
 }
 
 int dba_ba_host(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, const float* disps_sens,
@@ -1358,11 +1395,9 @@ int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t c
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   if (n == "dims") {
-    int32_t d[8] = {ctx->plan.n6, (ctx->plan.n6 + 1 + 3) & ~3, ctx->plan.Pp, ctx->plan.M, ctx->plan.S, ctx->plan_ppl,
-                    ctx->plan.degmax, ctx->plan.npairs_max};
-    if (cap < int64_t(sizeof(d))) return -1;
-    std::memcpy(host_out, d, sizeof(d));
-    return sizeof(d);
+    if (cap < int64_t(sizeof(ctx->last_dims))) return -1;
+    std::memcpy(host_out, ctx->last_dims, sizeof(ctx->last_dims));
+    return sizeof(ctx->last_dims);
   }
   if (n == "chi2") {               // double[iterations + 1] of the last call run with option "chi2": the objective before
                                   // every iteration and after the last one (per-edge partial sums added here, edge order)
@@ -1389,8 +1424,8 @@ int64_t dba_debug_read(dba_ctx* ctx, const char* name, void* host_out, int64_t c
   }
   if (n == "system") {
     if (!ctx->keep_system || !ctx->Akeep.p) return fail_arg(ctx, "keep_system option is off");
-    const int ld = (ctx->plan.n6 + 1 + 3) & ~3;
-    int64_t bytes = int64_t(ctx->plan.n6 + 1) * ld * sizeof(float);
+    const int ld = ctx->last_dims[1];
+    int64_t bytes = int64_t(ctx->last_dims[0] + 1) * ld * sizeof(float);
     if (cap < bytes) return -1;
     if (cudaMemcpy(host_out, ctx->Akeep.p, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
     return bytes;

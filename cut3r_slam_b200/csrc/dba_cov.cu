@@ -4,9 +4,14 @@
 // i.e. per pixel (k,p):  dzcov = Q^2 u^T S^-1 u + Q,  u = column (k,p) of E -- non-zero only in the 6-blocks of pose k
 // and of the poses k has edges to.  The reference forms F densely ([6P, M*HW]: 1.3 GB at 128 keyframes); here
 //   k_linv    W = L^-1 by 32-column blocks (one CTA per block column, forward substitution by blocks)
-//   k_wtw     S^-1 = W^T W (lower tiles, mirrored)
+//   k_wtw     S^-1 = W^T W (lower tiles, mirrored), summed and STORED in fp64
 //   k_dzcov   per (source keyframe, pixel tile): the columns of E are recomputed from the inputs (never stored),
-//             kept in shared memory, and the quadratic form runs over the (deg+1)^2 6x6 blocks of S^-1 it touches.
+//             kept in shared memory, and the quadratic form runs over the (deg+1)^2 6x6 blocks of S^-1 it touches,
+//             in fp64.  Why fp64 behind an fp32 W: u^T (W^T W) u cancels where |W u|^2 (the reference's sum of squares)
+//             does not -- with fp32 sums the rounding error is n eps rho^2 against the reference's 2 n eps rho,
+//             rho = || |W| |u| || / || W u || (measured 3.4x .. 4x the reference's own fp32 error on ill-conditioned
+//             ragged graphs, tests/test_ba_ragged_gpu.py); exact products of the fp32 entries summed in fp64 leave
+//             only W's own rounding, which enters both forms alike.
 #include "dba_kernels.h"
 #include "dba_math.cuh"
 
@@ -192,14 +197,14 @@ size_t linv_rl_smem(int nkb) {
 
 // Sinv = W^T W, lower tiles (a >= b) mirrored.  W is lower triangular by blocks: rows >= a only.
 __global__ void __launch_bounds__(256)
-k_wtw(const float* __restrict__ W, int ldw, int nkb, float* __restrict__ Sinv) {
+k_wtw(const float* __restrict__ W, int ldw, int nkb, double* __restrict__ Sinv) {
   __shared__ float sA[CB][CB + 1], sB[CB][CB + 1];
   int a = int((sqrtf(8.0f * float(blockIdx.x) + 1.0f) - 1.0f) * 0.5f);
   while ((a + 1) * (a + 2) / 2 <= int(blockIdx.x)) ++a;
   while (a * (a + 1) / 2 > int(blockIdx.x)) --a;
   const int b = int(blockIdx.x) - a * (a + 1) / 2;
   const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;     // outputs (i = ty + 8q, j = tx)
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
   for (int r = a; r < nkb; ++r) {
     for (int e = tid; e < CB * CB; e += 256) {
       const int i = e >> 5, j = e & 31;
@@ -209,9 +214,9 @@ k_wtw(const float* __restrict__ W, int ldw, int nkb, float* __restrict__ Sinv) {
     __syncthreads();
 #pragma unroll 8
     for (int k = 0; k < CB; ++k) {
-      const float bv = sB[k][tx];
+      const double bv = double(sB[k][tx]);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) acc[q] = fmaf(sA[k][ty + 8 * q], bv, acc[q]);
+      for (int q = 0; q < 4; ++q) acc[q] = fma(double(sA[k][ty + 8 * q]), bv, acc[q]);
     }
     __syncthreads();
   }
@@ -230,9 +235,9 @@ __global__ void
 k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
         const float* __restrict__ targets, const float* __restrict__ weights, const int32_t* __restrict__ kx,
         const int32_t* __restrict__ koff, const int32_t* __restrict__ cedge, const int32_t* __restrict__ cj, int HW, int wd,
-        int ntiles, int t0, int Pp, const float* __restrict__ Sinv, int lds, const float* __restrict__ Q,
+        int ntiles, int t0, int Pp, const double* __restrict__ Sinv, int lds, const float* __restrict__ Q,
         float* __restrict__ dzcov) {
-  extern __shared__ float smem[];
+  extern __shared__ __align__(16) float smem[];
   __shared__ float sRt[CV_CHUNK * 12], sAd[CV_CHUNK * 36];
   __shared__ int sedge[CV_CHUNK];
   const int PT = blockDim.x;
@@ -241,7 +246,7 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
   const int k = kx[m];
   const int e0 = koff[m], deg = koff[m + 1] - e0;
   float* su = smem;                                         // [(1 + deg) * 6][PT]
-  float* sS = smem + size_t(1 + deg) * 6 * PT;              // [(1 + deg)][36]
+  double* sS = reinterpret_cast<double*>(smem + size_t(1 + deg) * 6 * PT);   // [2][(1 + deg)][36], 8-byte aligned (PT % 32 == 0)
   int* sslot = reinterpret_cast<int*>(sS + size_t(1 + deg) * 72);
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
   const int p = tile * PT + tid;
@@ -305,56 +310,58 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
 #pragma unroll
   for (int c = 0; c < 6; ++c) su[size_t(c) * PT + tid] = ui[c];
   __syncthreads();
-  float quad = 0.f;
+  double quad = 0.0;
   // rows of S^-1 blocks for entry a: [b <= a][6][6], double-buffered -- the next row is in flight while this one is used
   const int rowlen = (1 + deg) * 36;
-  float* sSb[2] = {sS, sS + rowlen};
-  auto fetch = [&](int a, float* dst) {                     // cp.async: global -> shared without registers
+  double* sSb[2] = {sS, sS + rowlen};
+  auto fetch = [&](int a, double* dst) {                     // cp.async: global -> shared without registers
     const int sa = sslot[a];
     if (sa < 0) return;
     for (int e = tid; e < (a + 1) * 36; e += PT) {
       const int b = e / 36, rc = e - b * 36, r = rc / 6, c = rc - r * 6;
       const int sb = sslot[b];
-      const float* src = (sb >= 0) ? Sinv + int64_t(6 * sa + r) * lds + 6 * sb + c : Sinv;
+      const double* src = (sb >= 0) ? Sinv + int64_t(6 * sa + r) * lds + 6 * sb + c : Sinv;
       const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(dst + e));
-      const int sz = (sb >= 0) ? 4 : 0;                     // src-size 0: zero fill
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+      const int sz = (sb >= 0) ? 8 : 0;                     // src-size 0: zero fill
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
     }
   };
   fetch(0, sSb[0]);
   for (int a = 0; a <= deg; ++a) {
-    float* cur = sSb[a & 1];
+    double* cur = sSb[a & 1];
     asm volatile("cp.async.wait_all;\n" ::: "memory");
     __syncthreads();                                        // row a landed; everyone is done with the other buffer
     if (a + 1 <= deg) fetch(a + 1, sSb[(a + 1) & 1]);
     if (sslot[a] < 0) continue;                             // block-uniform: a fixed pose has no row in S
-    float ua[6];
+    double ua[6];
 #pragma unroll
-    for (int c = 0; c < 6; ++c) ua[c] = su[(size_t(a) * 6 + c) * PT + tid];
+    for (int c = 0; c < 6; ++c) ua[c] = double(su[(size_t(a) * 6 + c) * PT + tid]);
     // t = sum_{b<a} S_ab u_b + S_aa u_a / 2 ; quad += 2 u_a . t   (S symmetric: each off-diagonal pair once)
-    float t[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    double t[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (int b = 0; b <= a; ++b) {
-      const float4* Sb = reinterpret_cast<const float4*>(cur + b * 36);
-      float S[36];
+      const double2* Sb = reinterpret_cast<const double2*>(cur + b * 36);     // 16-byte aligned: 36 doubles per block
+      const double sc = (b == a) ? 0.5 : 1.0;
+      double ub[6];
 #pragma unroll
-      for (int q = 0; q < 9; ++q) { const float4 v = Sb[q]; S[4 * q] = v.x; S[4 * q + 1] = v.y; S[4 * q + 2] = v.z; S[4 * q + 3] = v.w; }
-      const float sc = (b == a) ? 0.5f : 1.0f;
-      float ub[6];
+      for (int c = 0; c < 6; ++c) ub[c] = sc * double(su[(size_t(b) * 6 + c) * PT + tid]);
 #pragma unroll
-      for (int c = 0; c < 6; ++c) ub[c] = sc * su[(size_t(b) * 6 + c) * PT + tid];
+      for (int r = 0; r < 6; ++r) {
 #pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int c = 0; c < 6; ++c) t[r] = fmaf(S[r * 6 + c], ub[c], t[r]);
+        for (int c2 = 0; c2 < 3; ++c2) {
+          const double2 v = Sb[r * 3 + c2];
+          t[r] = fma(v.x, ub[2 * c2], t[r]);
+          t[r] = fma(v.y, ub[2 * c2 + 1], t[r]);
+        }
+      }
     }
-    float dq = 0.f;
+    double dq = 0.0;
 #pragma unroll
-    for (int r = 0; r < 6; ++r) dq = fmaf(ua[r], t[r], dq);
-    quad = fmaf(2.f, dq, quad);
+    for (int r = 0; r < 6; ++r) dq = fma(ua[r], t[r], dq);
+    quad = fma(2.0, dq, quad);
   }
   if (inb) {
-    const float q = Q[int64_t(m) * HW + p];
-    dzcov[int64_t(m) * HW + p] = q * q * quad + q;
+    const double q = double(Q[int64_t(m) * HW + p]);
+    dzcov[int64_t(m) * HW + p] = float(q * q * quad + q);
   }
 }
 
@@ -362,7 +369,7 @@ k_dzcov(const float* __restrict__ poses, const float* __restrict__ disps, const 
 
 size_t cov_scratch_floats(int n) {
   const size_t npad = size_t((n + CB - 1) / CB) * CB;
-  return 2 * npad * npad;
+  return 3 * npad * npad;             // W (fp32) + S^-1 (fp64)
 }
 
 cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Workspace& ws, float* scratch,
@@ -370,7 +377,7 @@ cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Wor
   const int n = g.n6;
   const int nkb = (n + CB - 1) / CB, npad = nkb * CB;
   float* W = scratch;
-  float* Sinv = scratch + size_t(npad) * npad;
+  double* Sinv = reinterpret_cast<double*>(scratch + size_t(npad) * npad);   // npad % 32 == 0: 8-byte aligned
   cudaError_t err = cudaMemsetAsync(W, 0, size_t(npad) * npad * sizeof(float), st);
   if (err != cudaSuccess) return err;
   if (n > 0) {
@@ -388,7 +395,7 @@ cudaError_t launch_depth_cov(const DeviceGraph& g, const BAInputs& in, const Wor
   }
   if (g.M > 0) {
     int PT = 128;
-    auto bytes = [&](int pt) { return (size_t(1 + g.degmax) * 6 * pt + size_t(1 + g.degmax) * 73 + 8) * sizeof(float); };
+    auto bytes = [&](int pt) { return (size_t(1 + g.degmax) * 6 * pt + size_t(1 + g.degmax) * 145 + 8) * sizeof(float); };
     while (PT > 32 && bytes(PT) > (smem_cap > 12288 ? smem_cap - 12288 : 0)) PT >>= 1;
     if (bytes(PT) + 12288 > smem_cap) return cudaErrorInvalidConfiguration;
     err = cudaFuncSetAttribute(k_dzcov, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes(PT)));

@@ -176,3 +176,47 @@ def test_edges_without_weight():
     assert bool(torch.isfinite(g.disps).all()) and bool(torch.isfinite(g.poses).all())
     assert rel_err(g.disps.cpu(), disps64) < 1e-4
     assert float(ose3.tangent_update(g.poses.cpu().double(), poses64.double()).abs().max()) < 1e-4
+
+
+RAGGED_SUBSET = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "edges_inside_the_gauge", "degree_thresholds",
+                 "grid_below_one_tile", "self_edges", "random_101", "random_107"]
+
+
+@pytest.mark.parametrize("name", RAGGED_SUBSET)
+def test_depth_cov_on_ragged_graphs(name):
+    """dzcov of the same graphs (geom/ba.py:98-107, chol.py:74-76): rows follow unique(ii), not the frame index."""
+    db = _db()
+    p = make_problem(iters=1, **CASES[name])
+    g = p.to("cuda")
+    cov = db.depth_cov(g.poses, g.disps, g.intrinsics, None, g.targets, g.weights, g.eta, g.ii, g.jj, p.t0, p.t1, p.lm, p.ep)
+    ref = od.depth_cov(p.poses, p.disps, p.intrinsics, None, p.targets, p.weights, p.eta, p.ii, p.jj, p.t0, p.t1, p.lm, p.ep)
+    got = cov.cpu().double().reshape(ref.shape[0], -1)
+    assert got.shape == ref.reshape(ref.shape[0], -1).shape
+    assert float(((got - ref.reshape(ref.shape[0], -1)).abs() / ref.reshape(ref.shape[0], -1).abs()).max()) < 1e-4
+
+
+@pytest.mark.parametrize("name", RAGGED_SUBSET)
+def test_pgba_on_ragged_graphs(name):
+    """The Sim3 path (7-dof blocks, its own plan) on the same graphs, scales != 1, against oracle/pgba.py in fp64."""
+    import oracle.pgba as op
+    db = _db()
+    p = make_problem(iters=2, **CASES[name])
+    P = p.poses.shape[0]
+    s = 1.0 + 0.05 * (2 * torch.rand(P, 1, generator=torch.Generator().manual_seed(3)) - 1)
+    s[: p.t0] = 1.0
+    poses8 = torch.cat([p.poses, s], -1)
+    a = (poses8, p.disps, p.intrinsics, p.targets, p.weights, p.eta, p.ii, p.jj, None, None, None, None, p.t0, p.t1, 1,
+         p.lm, p.ep, 0.0)
+    p64, d64, i64 = op.oracle_pgba(*a, dtype=torch.float64, return_info=True)
+    p32, d32, i32 = op.oracle_pgba(*a, dtype=torch.float32, return_info=True)
+    e = torch.zeros(0, dtype=torch.int64, device="cuda")
+    Pg, Dg = poses8.cuda(), p.disps.cuda()
+    dx, dz = db.pgba(Pg, Dg, p.intrinsics.cuda(), p.targets.cuda(), p.weights.cuda(), p.eta.cuda(), p.ii.cuda(), p.jj.cuda(),
+                     e, e, torch.zeros(0, 7, device="cuda"), torch.zeros(0, 7, 7, device="cuda"), p.t0, p.t1, 1, p.lm, p.ep)
+    gap = rel_err(i32[0][0], i64[0][0])
+    assert rel_err(dx.cpu(), i64[0][0]) < MULT * gap + 1e-5, gap
+    assert rel_err(Dg.cpu(), d64) < max(1e-4, MULT * rel_err(d32, d64))
+    src = torch.zeros(P, dtype=torch.bool)
+    src[p.ii] = True
+    assert torch.equal(Dg.cpu()[~src], p.disps[~src])
+    assert torch.equal(Pg.cpu()[: p.t0], poses8[: p.t0])
