@@ -9,22 +9,38 @@ namespace dba {
 namespace {
 inline int tri(int a, int b) { return a * (a + 1) / 2 + b; }   // a >= b
 
-struct Placed { int32_t dst; Item it; };
+using Placed = PlanPlaced;
 
 // stable counting sort of placements by destination
-void bucket(const std::vector<Placed>& src, int ndst, std::vector<int32_t>& off, std::vector<Item>& items) {
+void bucket(const std::vector<Placed>& src, int ndst, std::vector<int32_t>& off, std::vector<Item>& items,
+            std::vector<int32_t>& cur) {
   off.assign(ndst + 1, 0);
   for (const auto& p : src) off[p.dst + 1]++;
   for (int i = 0; i < ndst; ++i) off[i + 1] += off[i];
   items.resize(src.size());
-  std::vector<int32_t> cur(off.begin(), off.end() - 1);
+  cur.assign(off.begin(), off.end() - 1);
   for (const auto& p : src) items[cur[p.dst]++] = p.it;
+}
+
+// back to the default state without giving the vectors' memory back
+void reset(Plan& P) {
+  P.E = P.N = P.t0 = P.t1 = P.Pp = P.M = P.n6 = 0;
+  P.S = 1;
+  P.motion_only = false;
+  P.degmax = P.nblkmax = P.npairs_max = 0;
+  P.slab_blocks = P.vE_blocks = 0;
+  P.nSblk = 0;
+  for (auto* v : {&P.kx, &P.koff, &P.cedge, &P.ci, &P.cj, &P.pairbase, &P.blkbase, &P.slot_of_frame, &P.sblk_off, &P.rhs_off})
+    v->clear();
+  P.sblk_items.clear(); P.rhs_items.clear();
+  P.key_ii.clear(); P.key_jj.clear();
+  P.error.clear();
 }
 }  // namespace
 
 bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int N, int t0, int t1,
                 bool motion_only, int64_t M_expected, int splits) {
-  P = Plan();
+  reset(P);
   if (E64 < 0 || E64 > (int64_t(1) << 24)) { P.error = "edge count out of range"; return false; }
   const int E = int(E64);
   if (N <= 0 || t0 < 0 || t1 > N || t1 - t0 <= 0) {
@@ -46,7 +62,8 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
 
   // kx = sorted unique(ii)  (ba.py:70)
   P.slot_of_frame.assign(N, -1);
-  std::vector<int32_t> deg_of_frame(N, 0);
+  std::vector<int32_t>& deg_of_frame = P.scratch_deg;
+  deg_of_frame.assign(N, 0);
   for (int e = 0; e < E; ++e) deg_of_frame[ii[e]]++;
   for (int f = 0; f < N; ++f)
     if (deg_of_frame[f] > 0) { P.slot_of_frame[f] = int32_t(P.kx.size()); P.kx.push_back(f); }
@@ -60,7 +77,8 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
   for (int m = 0; m < P.M; ++m) P.koff[m + 1] = P.koff[m] + deg_of_frame[P.kx[m]];
   P.cedge.resize(E); P.ci.resize(E); P.cj.resize(E);
   {
-    std::vector<int32_t> cur(P.koff.begin(), P.koff.end() - 1);
+    std::vector<int32_t>& cur = P.scratch_cur;
+    cur.assign(P.koff.begin(), P.koff.end() - 1);
     for (int e = 0; e < E; ++e) {
       int m = P.slot_of_frame[ii[e]];
       int c = cur[m]++;
@@ -85,7 +103,9 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
   P.nSblk = P.Pp * (P.Pp + 1) / 2;
 
   // ---- gather lists --------------------------------------------------------------------------
-  std::vector<Placed> sp, rp;
+  std::vector<Placed>& sp = P.scratch_s;
+  std::vector<Placed>& rp = P.scratch_r;
+  sp.clear(); rp.clear();
   sp.reserve(size_t(4) * E + size_t(P.pairbase[P.M]) * 2);
   rp.reserve(size_t(2) * E + size_t(P.blkbase[P.M]));
   auto inr = [&](int p) { return p >= 0 && p < P.Pp; };
@@ -126,8 +146,8 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
       }
     }
   }
-  bucket(sp, P.nSblk, P.sblk_off, P.sblk_items);
-  bucket(rp, P.Pp, P.rhs_off, P.rhs_items);
+  bucket(sp, P.nSblk, P.sblk_off, P.sblk_items, P.scratch_cur);
+  bucket(rp, P.Pp, P.rhs_off, P.rhs_items, P.scratch_cur);
   return true;
 }
 
