@@ -306,6 +306,26 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
         const int cand_s = (cand < cand_lo) ? one_wave : cand;       // the extra first round tries the one-wave split
         const int tps_c = (ntilesT + cand_s - 1) / cand_s, S_c = (ntilesT + tps_c - 1) / tps_c;
         if (S_c != cand_s) { continue; }
+        {
+          // no schedule beats total work / slots (nor its longest job): a candidate whose bound already loses is not
+          // simulated (same choice as without the test; the simulation is ~0.3 ms of host time per new graph otherwise)
+          double work = 0.0, longest = 0.0;
+          const int nt_last = ntilesT - (S_c - 1) * tps_c;
+          auto job = [&](int dgk, bool is_wide, int nt) {
+            if (use_v2) return 1.4 + nt * (is_wide ? 0.1 * (dgk + 1.0) : 1.0 + 0.03 * dgk);
+            return 4.0 + nt * (is_wide ? 0.064 * (dgk + 1.0) * (dgk + 1.0) : dgk + 6.0);
+          };
+          for (int dgk : wide) {
+            work += ((S_c - 1) * job(dgk, true, tps_c) + job(dgk, true, nt_last)) * (use_v2 ? 1.0 : 2.0);
+            longest = std::max(longest, job(dgk, true, tps_c));
+          }
+          for (int dgk : degs) {
+            work += (S_c - 1) * job(dgk, false, tps_c) + job(dgk, false, nt_last);
+            longest = std::max(longest, job(dgk, false, tps_c));
+          }
+          const double bound = std::max(work / slots, longest) * (1.0 - 1e-9);
+          if (bound * (1.0 + 0.01 * S_c) >= best) continue;
+        }
         std::priority_queue<double, std::vector<double>, std::greater<double>> free_at;
         for (int i = 0; i < slots; ++i) free_at.push(0.0);
         double makespan = 0.0;
@@ -412,12 +432,12 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   size_t o_bl = put(blist);
   CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
   CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
-  std::vector<Item> items(P.sblk_items);
-  const size_t n_s = items.size();
-  items.insert(items.end(), P.rhs_items.begin(), P.rhs_items.end());
-  CK(ctx->d_items.ensure(items.size() * sizeof(Item) + 16), "plan alloc");
-  if (!items.empty())
-    CK(cudaMemcpyAsync(ctx->d_items.p, items.data(), items.size() * sizeof(Item), cudaMemcpyHostToDevice, st),
+  const size_t n_s = P.sblk_items.size(), n_r = P.rhs_items.size();
+  CK(ctx->d_items.ensure((n_s + n_r) * sizeof(Item) + 16), "plan alloc");
+  if (n_s)
+    CK(cudaMemcpyAsync(ctx->d_items.p, P.sblk_items.data(), n_s * sizeof(Item), cudaMemcpyHostToDevice, st), "plan upload");
+  if (n_r)
+    CK(cudaMemcpyAsync(ctx->d_items.as<Item>() + n_s, P.rhs_items.data(), n_r * sizeof(Item), cudaMemcpyHostToDevice, st),
        "plan upload");
   CK(cudaStreamSynchronize(st), "plan upload");   // host vectors go out of scope
 

@@ -9,19 +9,6 @@ namespace dba {
 namespace {
 inline int tri(int a, int b) { return a * (a + 1) / 2 + b; }   // a >= b
 
-using Placed = PlanPlaced;
-
-// stable counting sort of placements by destination
-void bucket(const std::vector<Placed>& src, int ndst, std::vector<int32_t>& off, std::vector<Item>& items,
-            std::vector<int32_t>& cur) {
-  off.assign(ndst + 1, 0);
-  for (const auto& p : src) off[p.dst + 1]++;
-  for (int i = 0; i < ndst; ++i) off[i + 1] += off[i];
-  items.resize(src.size());
-  cur.assign(off.begin(), off.end() - 1);
-  for (const auto& p : src) items[cur[p.dst]++] = p.it;
-}
-
 // back to the default state without giving the vectors' memory back
 void reset(Plan& P) {
   P.E = P.N = P.t0 = P.t1 = P.Pp = P.M = P.n6 = 0;
@@ -103,51 +90,73 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
   P.nSblk = P.Pp * (P.Pp + 1) / 2;
 
   // ---- gather lists --------------------------------------------------------------------------
-  std::vector<Placed>& sp = P.scratch_s;
-  std::vector<Placed>& rp = P.scratch_r;
-  sp.clear(); rp.clear();
-  sp.reserve(size_t(4) * E + size_t(P.pairbase[P.M]) * 2);
-  rp.reserve(size_t(2) * E + size_t(P.blkbase[P.M]));
-  auto inr = [&](int p) { return p >= 0 && p < P.Pp; };
-  // per-edge blocks (ba.py:73-82,86-88): which = 0 Hii, 1 Hij, 2 Hji, 3 Hjj ; v: 0 vi, 1 vj
-  for (int c = 0; c < E; ++c) {
-    int i = P.ci[c] - t0, j = P.cj[c] - t0;
-    if (inr(i)) {
-      sp.push_back({tri(i, i), Item{0, c * 4 + 0, 0, 0}});
-      rp.push_back({i, Item{0, c * 2 + 0, 0, 0}});
-    }
-    if (inr(j)) {
-      sp.push_back({tri(j, j), Item{0, c * 4 + 3, 0, 0}});
-      rp.push_back({j, Item{0, c * 2 + 1, 0, 0}});
-    }
-    if (inr(i) && inr(j)) {
-      if (i >= j) sp.push_back({tri(i, j), Item{0, c * 4 + 1, 0, 0}});   // Hij at (i,j)
-      if (j >= i) sp.push_back({tri(j, i), Item{0, c * 4 + 2, 0, 0}});   // Hji at (j,i)
-    }
-  }
-  if (!motion_only) {
-    // Schur products (chol.py:63-64): keyframe slot m, panel blocks A >= B
-    for (int m = 0; m < P.M; ++m) {
-      int e0 = P.koff[m], deg = P.koff[m + 1] - e0, nblk = deg + 1;
-      int npairs = nblk * (nblk + 1) / 2;
-      auto pose_of = [&](int b) { return (b == 0 ? P.kx[m] : P.cj[e0 + b - 1]) - t0; };
-      for (int A = 0; A < nblk; ++A) {
-        int pA = pose_of(A);
-        if (!inr(pA)) continue;
-        for (int B = 0; B <= A; ++B) {
-          int pB = pose_of(B);
-          if (!inr(pB)) continue;
-          int32_t base = int32_t(int64_t(P.pairbase[m]) * P.S + tri(A, B));
-          // X = E_A Q E_B^T sits at (pA,pB); X^T at (pB,pA) when A != B
-          if (pA >= pB) sp.push_back({tri(pA, pB), Item{1, base, npairs, 0}});
-          if (A != B && pB >= pA) sp.push_back({tri(pB, pA), Item{1 | 2, base, npairs, 0}});
-        }
-        rp.push_back({pA, Item{1, int32_t(int64_t(P.blkbase[m]) * P.S + A), nblk, 0}});
+  // Two walks over the same contributions in the same order: the first counts per destination block, the second
+  // places every item at its final position (a stable counting sort without the intermediate list).
+  const int Pp = P.Pp, S = P.S;
+  const int32_t* ci = P.ci.data();
+  const int32_t* cj = P.cj.data();
+  auto walk = [&](auto&& to_S, auto&& to_rhs) {
+    // per-edge blocks (ba.py:73-82,86-88): which = 0 Hii, 1 Hij, 2 Hji, 3 Hjj ; v: 0 vi, 1 vj
+    for (int c = 0; c < E; ++c) {
+      const int i = ci[c] - t0, j = cj[c] - t0;
+      const bool oi = i >= 0 && i < Pp, oj = j >= 0 && j < Pp;
+      if (oi) {
+        to_S(tri(i, i), Item{0, c * 4 + 0, 0, 0});
+        to_rhs(i, Item{0, c * 2 + 0, 0, 0});
+      }
+      if (oj) {
+        to_S(tri(j, j), Item{0, c * 4 + 3, 0, 0});
+        to_rhs(j, Item{0, c * 2 + 1, 0, 0});
+      }
+      if (oi && oj) {
+        if (i >= j) to_S(tri(i, j), Item{0, c * 4 + 1, 0, 0});   // Hij at (i,j)
+        if (j >= i) to_S(tri(j, i), Item{0, c * 4 + 2, 0, 0});   // Hji at (j,i)
       }
     }
+    if (motion_only) return;
+    // Schur products (chol.py:63-64): keyframe slot m, panel blocks A >= B
+    for (int m = 0; m < P.M; ++m) {
+      const int e0 = P.koff[m], deg = P.koff[m + 1] - e0, nblk = deg + 1;
+      const int npairs = nblk * (nblk + 1) / 2;
+      const int k0 = P.kx[m] - t0;
+      const int64_t pb = int64_t(P.pairbase[m]) * S, bb = int64_t(P.blkbase[m]) * S;
+      for (int A = 0; A < nblk; ++A) {
+        const int pA = (A == 0) ? k0 : cj[e0 + A - 1] - t0;
+        if (pA < 0 || pA >= Pp) continue;
+        for (int B = 0; B <= A; ++B) {
+          const int pB = (B == 0) ? k0 : cj[e0 + B - 1] - t0;
+          if (pB < 0 || pB >= Pp) continue;
+          const int32_t base = int32_t(pb + tri(A, B));
+          // X = E_A Q E_B^T sits at (pA,pB); X^T at (pB,pA) when A != B
+          if (pA >= pB) to_S(tri(pA, pB), Item{1, base, npairs, 0});
+          if (A != B && pB >= pA) to_S(tri(pB, pA), Item{1 | 2, base, npairs, 0});
+        }
+        to_rhs(pA, Item{1, int32_t(bb + A), nblk, 0});
+      }
+    }
+  };
+  P.sblk_off.assign(P.nSblk + 1, 0);
+  P.rhs_off.assign(Pp + 1, 0);
+  {
+    int32_t* so = P.sblk_off.data() + 1;
+    int32_t* ro = P.rhs_off.data() + 1;
+    walk([&](int dst, const Item&) { so[dst]++; }, [&](int dst, const Item&) { ro[dst]++; });
   }
-  bucket(sp, P.nSblk, P.sblk_off, P.sblk_items, P.scratch_cur);
-  bucket(rp, P.Pp, P.rhs_off, P.rhs_items, P.scratch_cur);
+  for (int i = 0; i < P.nSblk; ++i) P.sblk_off[i + 1] += P.sblk_off[i];
+  for (int i = 0; i < Pp; ++i) P.rhs_off[i + 1] += P.rhs_off[i];
+  P.sblk_items.resize(size_t(P.sblk_off[P.nSblk]));
+  P.rhs_items.resize(size_t(P.rhs_off[Pp]));
+  {
+    std::vector<int32_t>& cs = P.scratch_cur;
+    std::vector<int32_t>& cr = P.scratch_deg;
+    cs.assign(P.sblk_off.begin(), P.sblk_off.end() - 1);
+    cr.assign(P.rhs_off.begin(), P.rhs_off.end() - 1);
+    Item* si = P.sblk_items.data();
+    Item* ri = P.rhs_items.data();
+    int32_t* csp = cs.data();
+    int32_t* crp = cr.data();
+    walk([&](int dst, const Item& it) { si[csp[dst]++] = it; }, [&](int dst, const Item& it) { ri[crp[dst]++] = it; });
+  }
   return true;
 }
 

@@ -20,8 +20,6 @@ struct Item {       // one contribution to a 6x6 block of S or a 6-vector of the
   int32_t pad;
 };
 
-struct PlanPlaced { int32_t dst; Item it; };   // build_plan scratch: one contribution and the block it lands in
-
 struct Plan {
   // problem shape
   int E = 0, N = 0, t0 = 0, t1 = 0, Pp = 0, M = 0, n6 = 0, S = 1;
@@ -38,9 +36,8 @@ struct Plan {
   // identity of the graph this plan was built for (cache key)
   std::vector<int64_t> key_ii, key_jj;
   std::string error;
-  // build_plan scratch, kept between builds of the same Plan object: a SLAM loop rebuilds the plan on every new edge
-  // list, and fresh multi-megabyte vectors cost more in page faults than the plan costs to compute
-  std::vector<PlanPlaced> scratch_s, scratch_r;
+  // build_plan scratch (cursors / degree counts), kept between builds of the same Plan object: a SLAM loop rebuilds
+  // the plan on every new edge list
   std::vector<int32_t> scratch_cur, scratch_deg;
 };
 
