@@ -7,7 +7,9 @@
 #include <nvtx3/nvToolsExt.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <functional>
 #include <queue>
@@ -238,6 +240,10 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   }
   ctx->plan_valid = false;
   ++ctx->graph_epoch;
+  // DBA_PLAN_TRACE=1: host time of the rebuild's sections on stderr (developer diagnostic for the cold-plan path)
+  static const bool trace = std::getenv("DBA_PLAN_TRACE") != nullptr;
+  auto now_us = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  double tr_t[5] = {now_us(), 0, 0, 0, 0};
   if (E > 0) {
     for (int64_t e = 0; e < E; ++e)
       if (ii[e] < 0 || ii[e] >= N) return fail_arg(ctx, "edge index outside the frame buffer");
@@ -384,7 +390,9 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   if (S < 1) S = 1;
   const int tps = (ntilesT + S - 1) / S;
   S = (ntilesT + tps - 1) / tps;     // no empty split
+  tr_t[1] = now_us();
   if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
+  tr_t[2] = now_us();
   ctx->plan_v2 = use_v2;
   ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW; ctx->plan_ht = ht; ctx->plan_wd = wd;
 
@@ -430,6 +438,7 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   const int n_light = int(blist.size());
   blist.insert(blist.end(), heavy.begin(), heavy.end());
   size_t o_bl = put(blist);
+  tr_t[3] = now_us();
   CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
   CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
   const size_t n_s = P.sblk_items.size(), n_r = P.rhs_items.size();
@@ -440,6 +449,10 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
     CK(cudaMemcpyAsync(ctx->d_items.as<Item>() + n_s, P.rhs_items.data(), n_r * sizeof(Item), cudaMemcpyHostToDevice, st),
        "plan upload");
   CK(cudaStreamSynchronize(st), "plan upload");   // host vectors go out of scope
+  tr_t[4] = now_us();
+  if (trace)
+    std::fprintf(stderr, "[dba plan] E=%lld S=%d: split choice %.0f us, build_plan %.0f us, lists + pack %.0f us, upload + sync %.0f us\n",
+                 (long long)E, S, tr_t[1] - tr_t[0], tr_t[2] - tr_t[1], tr_t[3] - tr_t[2], tr_t[4] - tr_t[3]);
 
   DeviceGraph& g = ctx->g;
   const int32_t* base = ctx->d_plan_i32.as<int32_t>();
