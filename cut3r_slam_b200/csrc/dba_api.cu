@@ -107,10 +107,10 @@ struct dba_ctx {
   // ba and depth_cov calls alternating on one graph rebuild neither plan (swap_plan_slot)
   struct PlanSlot {
     Plan plan;
-    bool valid = false, v2 = false;
+    bool valid = false, v2 = false, pending = false;
     int ppl = 0, tps = 1, HW = 0, ht = 0, wd = 0;
     uint64_t key = 0;
-    DevBuf i32, items;
+    DevBuf i32, i32b, items;
     DeviceGraph g{};
   } cov_slot;
   int32_t last_dims[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // of the plan the last call ran on (debug_read "dims")
@@ -129,6 +129,12 @@ struct dba_ctx {
   // host staging
   int64_t* h_idx = nullptr;
   size_t h_idx_cap = 0;
+  char* h_plan[2] = {nullptr, nullptr};   // pinned staging of the plan upload, one region per half (pageable copies of
+  size_t h_plan_cap[2] = {0, 0};          // the loop-closure plan's 3.7 MB of items took 1.4 - 3.4 ms)
+  cudaEvent_t ev_plan = nullptr;          // behind the last upload: the staging regions are free again
+  std::vector<int32_t> h_pack;            // packing scratch of the uploads
+  bool plan_gather_pending = false;       // the plan's CSR half is on the device, its gather lists are not built yet
+  DevBuf d_plan_i32b;                     // offsets / block list of the gather half (d_plan_i32 holds the CSR half)
   // host-entry staging (dba_ba_host)
   DevBuf s_poses, s_disps, s_intr, s_sens, s_targets, s_weights, s_eta, s_ii, s_jj, s_dx, s_dz;
   // proj_trans: CSR of the edges by source keyframe (cached by the edge lists)
@@ -203,9 +209,20 @@ int fail_cuda(dba_ctx* c, cudaError_t e, const char* where) {
 void swap_plan_slot(dba_ctx* c) {
   auto& a = c->cov_slot;
   std::swap(c->plan, a.plan); std::swap(c->plan_valid, a.valid); std::swap(c->plan_v2, a.v2);
+  std::swap(c->plan_gather_pending, a.pending);
   std::swap(c->plan_ppl, a.ppl); std::swap(c->plan_tps, a.tps); std::swap(c->plan_HW, a.HW);
   std::swap(c->plan_ht, a.ht); std::swap(c->plan_wd, a.wd); std::swap(c->plan_key, a.key);
-  std::swap(c->d_plan_i32, a.i32); std::swap(c->d_items, a.items); std::swap(c->g, a.g);
+  std::swap(c->d_plan_i32, a.i32); std::swap(c->d_plan_i32b, a.i32b); std::swap(c->d_items, a.items); std::swap(c->g, a.g);
+}
+
+cudaError_t plan_staging(dba_ctx* c, size_t bytes, int region) {
+  if (bytes <= c->h_plan_cap[region]) return cudaSuccess;
+  if (c->h_plan[region]) cudaFreeHost(c->h_plan[region]);
+  c->h_plan[region] = nullptr; c->h_plan_cap[region] = 0;
+  const size_t want = bytes + bytes / 4;
+  cudaError_t e = cudaMallocHost(&c->h_plan[region], want);
+  if (e == cudaSuccess) c->h_plan_cap[region] = want;
+  return e;
 }
 
 int out_degree_max(const int64_t* ii, int64_t E, int N, int* M_out) {
@@ -391,7 +408,9 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   const int tps = (ntilesT + S - 1) / S;
   S = (ntilesT + tps - 1) / tps;     // no empty split
   tr_t[1] = now_us();
-  if (!build_plan(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
+  // first half of the plan: what the linearisation needs.  The gather lists of the assembly (finish_plan) are built
+  // while the first linearisation of the new graph runs
+  if (!build_plan_csr(P, ii, jj, E, N, t0, t1, motion_only, M, S)) return fail_arg(ctx, P.error);
   tr_t[2] = now_us();
   ctx->plan_v2 = use_v2;
   ctx->plan_ppl = ppl; ctx->plan_tps = tps; ctx->plan_HW = HW; ctx->plan_ht = ht; ctx->plan_wd = wd;
@@ -419,8 +438,9 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   std::vector<int32_t> nonsrc;
   for (int f = 0; f < t1; ++f) if (P.slot_of_frame[f] < 0) nonsrc.push_back(f);
 
-  // pack all int32 arrays into one upload
-  std::vector<int32_t> pack;
+  // pack the int32 arrays of this half into one upload
+  std::vector<int32_t>& pack = ctx->h_pack;
+  pack.clear();
   auto put = [&](const std::vector<int32_t>& v) {
     size_t off = pack.size();
     pack.insert(pack.end(), v.begin(), v.end());
@@ -428,31 +448,18 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
     return off;
   };
   size_t o_kx = put(P.kx), o_koff = put(P.koff), o_cedge = put(P.cedge), o_ci = put(P.ci), o_cj = put(P.cj);
-  size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc), o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
+  size_t o_pb = put(P.pairbase), o_bb = put(P.blkbase), o_ns = put(nonsrc);
   size_t o_tc = put(tc_list), o_sl = put(simt_list), o_wl = put(wide_list), o_wl2 = put(wide2_list);
-  std::vector<int32_t> blist, heavy;
-  // small systems: every block gets its own CTA (8 item lanes); large ones: blocks with <= 8 items share a CTA
-  const bool all_heavy = P.nSblk <= 1184;
-  for (int ob = 0; ob < P.nSblk; ++ob)
-    (!all_heavy && P.sblk_off[ob + 1] - P.sblk_off[ob] <= 8 ? blist : heavy).push_back(ob);
-  const int n_light = int(blist.size());
-  blist.insert(blist.end(), heavy.begin(), heavy.end());
-  size_t o_bl = put(blist);
   tr_t[3] = now_us();
   CK(ctx->d_plan_i32.ensure(pack.size() * 4 + 16), "plan alloc");
-  CK(cudaMemcpyAsync(ctx->d_plan_i32.p, pack.data(), pack.size() * 4, cudaMemcpyHostToDevice, st), "plan upload");
-  const size_t n_s = P.sblk_items.size(), n_r = P.rhs_items.size();
-  CK(ctx->d_items.ensure((n_s + n_r) * sizeof(Item) + 16), "plan alloc");
-  if (n_s)
-    CK(cudaMemcpyAsync(ctx->d_items.p, P.sblk_items.data(), n_s * sizeof(Item), cudaMemcpyHostToDevice, st), "plan upload");
-  if (n_r)
-    CK(cudaMemcpyAsync(ctx->d_items.as<Item>() + n_s, P.rhs_items.data(), n_r * sizeof(Item), cudaMemcpyHostToDevice, st),
-       "plan upload");
-  CK(cudaStreamSynchronize(st), "plan upload");   // host vectors go out of scope
-  tr_t[4] = now_us();
-  if (trace)
-    std::fprintf(stderr, "[dba plan] E=%lld S=%d: split choice %.0f us, build_plan %.0f us, lists + pack %.0f us, upload + sync %.0f us\n",
-                 (long long)E, S, tr_t[1] - tr_t[0], tr_t[2] - tr_t[1], tr_t[3] - tr_t[2], tr_t[4] - tr_t[3]);
+  const size_t b_pack = pack.size() * 4;
+  // pinned staging, two regions: [this half | the gather half]; the previous rebuild's copies have left it
+  if (ctx->ev_plan) CK(cudaEventSynchronize(ctx->ev_plan), "plan upload");
+  CK(plan_staging(ctx, b_pack + 64, 0), "pinned staging");
+  std::memcpy(ctx->h_plan[0], pack.data(), b_pack);
+  if (b_pack) CK(cudaMemcpyAsync(ctx->d_plan_i32.p, ctx->h_plan[0], b_pack, cudaMemcpyHostToDevice, st), "plan upload");
+  if (!ctx->ev_plan) CK(cudaEventCreateWithFlags(&ctx->ev_plan, cudaEventDisableTiming), "plan upload");
+  CK(cudaEventRecord(ctx->ev_plan, st), "plan upload");       // re-recorded behind the gather half's copies
 
   DeviceGraph& g = ctx->g;
   const int32_t* base = ctx->d_plan_i32.as<int32_t>();
@@ -461,16 +468,70 @@ int prepare_plan(dba_ctx* ctx, const int64_t* ii, const int64_t* jj, int64_t E, 
   g.HW = HW; g.ht = ht; g.wd = wd;
   g.kx = base + o_kx; g.koff = base + o_koff; g.cedge = base + o_cedge; g.ci = base + o_ci; g.cj = base + o_cj;
   g.pairbase = base + o_pb; g.blkbase = base + o_bb; g.nonsrc = base + o_ns; g.n_nonsrc = int(nonsrc.size());
-  g.sblk_off = base + o_so; g.rhs_off = base + o_ro;
   g.tc_list = base + o_tc; g.simt_list = base + o_sl; g.n_tc = int(tc_list.size()); g.n_simt = int(simt_list.size());
   g.degmax_tc = degmax_tc;
   g.wide_list = base + o_wl; g.n_wide = int(wide_list.size()); g.degmax_wide = degmax_wide;
   g.wide2_list = base + o_wl2; g.n_wide2 = int(wide2_list.size()); g.degmax_wide2 = degmax_wide2;
+  g.nSblk = P.nSblk;
+  g.sblk_off = nullptr; g.rhs_off = nullptr; g.sblk_items = nullptr; g.rhs_items = nullptr; g.sblk_list = nullptr; g.n_light = 0;
+  ctx->plan_gather_pending = true;     // plan_valid stays false until finish_plan has run
+  tr_t[4] = now_us();
+  if (trace)
+    std::fprintf(stderr, "[dba plan] E=%lld S=%d: split choice %.0f us, CSR half %.0f us, kernel lists + pack %.0f us, upload %.0f us\n",
+                 (long long)E, S, tr_t[1] - tr_t[0], tr_t[2] - tr_t[1], tr_t[3] - tr_t[2], tr_t[4] - tr_t[3]);
+  return 0;
+}
+
+// second half of a rebuilt plan: the gather lists of the assembly, uploaded on `st` (run_ba calls it behind the launches
+// of the new graph's first linearisation, so the host work overlaps that kernel)
+int finish_plan(dba_ctx* ctx, cudaStream_t st) {
+  if (!ctx->plan_gather_pending) return 0;
+  static const bool trace = std::getenv("DBA_PLAN_TRACE") != nullptr;
+  auto now_us = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_a = now_us();
+  Plan& P = ctx->plan;
+  build_plan_gather(P);
+  const double t_b = now_us();
+  std::vector<int32_t>& pack = ctx->h_pack;
+  pack.clear();
+  auto put = [&](const std::vector<int32_t>& v) {
+    size_t off = pack.size();
+    pack.insert(pack.end(), v.begin(), v.end());
+    while (pack.size() % 4) pack.push_back(0);
+    return off;
+  };
+  size_t o_so = put(P.sblk_off), o_ro = put(P.rhs_off);
+  std::vector<int32_t> blist, heavy;
+  // small systems: every block gets its own CTA (8 item lanes); large ones: blocks with <= 8 items share a CTA
+  const bool all_heavy = P.nSblk <= 1184;
+  for (int ob = 0; ob < P.nSblk; ++ob)
+    (!all_heavy && P.sblk_off[ob + 1] - P.sblk_off[ob] <= 8 ? blist : heavy).push_back(ob);
+  const int n_light = int(blist.size());
+  blist.insert(blist.end(), heavy.begin(), heavy.end());
+  size_t o_bl = put(blist);
+  const size_t n_s = P.sblk_items.size(), n_r = P.rhs_items.size();
+  const size_t b_pack = pack.size() * 4, b_s = n_s * sizeof(Item), b_r = n_r * sizeof(Item);
+  CK(ctx->d_plan_i32b.ensure(b_pack + 16), "plan alloc");
+  CK(ctx->d_items.ensure(b_s + b_r + 16), "plan alloc");
+  CK(plan_staging(ctx, b_pack + b_s + b_r + 64, 1), "pinned staging");
+  char* h = ctx->h_plan[1];
+  std::memcpy(h, pack.data(), b_pack);
+  if (b_s) std::memcpy(h + b_pack, P.sblk_items.data(), b_s);
+  if (b_r) std::memcpy(h + b_pack + b_s, P.rhs_items.data(), b_r);
+  if (b_pack) CK(cudaMemcpyAsync(ctx->d_plan_i32b.p, h, b_pack, cudaMemcpyHostToDevice, st), "plan upload");
+  if (b_s + b_r) CK(cudaMemcpyAsync(ctx->d_items.p, h + b_pack, b_s + b_r, cudaMemcpyHostToDevice, st), "plan upload");
+  CK(cudaEventRecord(ctx->ev_plan, st), "plan upload");       // the staging regions are free again behind this
+  DeviceGraph& g = ctx->g;
+  const int32_t* base = ctx->d_plan_i32b.as<int32_t>();
+  g.sblk_off = base + o_so; g.rhs_off = base + o_ro;
   g.sblk_items = ctx->d_items.as<Item>();
   g.rhs_items = ctx->d_items.as<Item>() + n_s;
-  g.nSblk = P.nSblk;
   g.sblk_list = base + o_bl; g.n_light = n_light;
+  ctx->plan_gather_pending = false;
   ctx->plan_valid = true;
+  if (trace)
+    std::fprintf(stderr, "[dba plan]   gather half (behind the first linearisation): lists %.0f us, pack + upload %.0f us\n",
+                 t_b - t_a, now_us() - t_b);
   return 0;
 }
 
@@ -528,6 +589,7 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
   Workspace ws{};
   rc = ensure_workspace(ctx, ws);
   if (rc) return rc;
+  if (ctx->plan_gather_pending && iterations <= 0) { rc = finish_plan(ctx, st); if (rc) return rc; }
   // ---- whole-call CUDA graph: a call that repeats an earlier one exactly (plan hit by the caller's key, same
   // buffers, same scalars) is captured once and then replayed with ONE launch.  What this buys is launch latency:
   // the frontend / motion-only windows are 12-13 dependent kernels of 5-40 us per LM iteration.
@@ -676,6 +738,8 @@ int run_ba(dba_ctx* ctx, float* poses, float* disps, const float* intr, const fl
       }
     }
     mark();
+    // a rebuilt plan: its gather lists are made now, on the host, while the linearisation above runs
+    if (ctx->plan_gather_pending) { rc = finish_plan(ctx, st); if (rc) return rc; }
     const bool sharded = ctx->comm != nullptr && ctx->nranks > 1;
     const bool p2p_fits = sharded && ctx->p2p_ok && ctx->opt_p2p && size_t(g.n6 + 1) * ws.ldA <= ctx->p2p_slab_floats;
     // measured on loopclosure (n = 3060): 2 GPUs 17.69 ms against 18.05 with the packed ncclAllReduce; 4 GPUs 14.53
@@ -833,7 +897,7 @@ void dba_destroy(dba_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-  DevBuf* bufs[] = {&c->d_plan_i32, &c->d_items, &c->cov_slot.i32, &c->cov_slot.items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
+  DevBuf* bufs[] = {&c->d_plan_i32, &c->d_plan_i32b, &c->d_items, &c->cov_slot.i32, &c->cov_slot.i32b, &c->cov_slot.items, &c->Hpart, &c->Spart, &c->vEpart, &c->Q, &c->w, &c->Hblk, &c->vblk,
                     &c->A, &c->Lm, &c->Ldiag, &c->dx, &c->dz, &c->fail, &c->Akeep, &c->solve_msg, &c->solve_flag, &c->d_chi2, &c->s_poses, &c->s_disps, &c->s_intr,
                     &c->s_sens, &c->s_targets, &c->s_weights, &c->s_eta, &c->s_ii, &c->s_jj, &c->s_dx, &c->s_dz, &c->d_pt, &c->d_jd, &c->d_cov, &c->d_slot, &c->d_pack, &c->pg_i32, &c->pg_items, &c->pg_H, &c->pg_v, &c->pg_Ep,
                     &c->pg_CW, &c->pg_Q, &c->pg_W, &c->pg_Eis, &c->pg_S, &c->pg_vE, &c->pg_Hsp, &c->pg_vsp, &c->pg_A, &c->pg_Lm,
@@ -848,6 +912,8 @@ void dba_destroy(dba_ctx* c) {
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->h_idx) cudaFreeHost(c->h_idx);
+  for (char* hp : c->h_plan) if (hp) cudaFreeHost(hp);
+  if (c->ev_plan) cudaEventDestroy(c->ev_plan);
   delete c;
 }
 

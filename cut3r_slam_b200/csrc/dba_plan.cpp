@@ -27,6 +27,13 @@ void reset(Plan& P) {
 
 bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int N, int t0, int t1,
                 bool motion_only, int64_t M_expected, int splits) {
+  if (!build_plan_csr(P, ii, jj, E64, N, t0, t1, motion_only, M_expected, splits)) return false;
+  build_plan_gather(P);
+  return true;
+}
+
+bool build_plan_csr(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int N, int t0, int t1,
+                    bool motion_only, int64_t M_expected, int splits) {
   reset(P);
   if (E64 < 0 || E64 > (int64_t(1) << 24)) { P.error = "edge count out of range"; return false; }
   const int E = int(E64);
@@ -89,6 +96,12 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
   P.vE_blocks = motion_only ? 0 : int64_t(P.blkbase[P.M]) * P.S;
   P.nSblk = P.Pp * (P.Pp + 1) / 2;
 
+  return true;
+}
+
+void build_plan_gather(Plan& P) {
+  const int E = P.E, t0 = P.t0;
+  const bool motion_only = P.motion_only;
   // ---- gather lists --------------------------------------------------------------------------
   // Two walks over the same contributions in the same order: the first counts per destination block, the second
   // places every item at its final position (a stable counting sort without the intermediate list).
@@ -157,7 +170,6 @@ bool build_plan(Plan& P, const int64_t* ii, const int64_t* jj, int64_t E64, int 
     int32_t* crp = cr.data();
     walk([&](int dst, const Item& it) { si[csp[dst]++] = it; }, [&](int dst, const Item& it) { ri[crp[dst]++] = it; });
   }
-  return true;
 }
 
 }  // namespace dba

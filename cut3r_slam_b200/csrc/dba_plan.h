@@ -45,5 +45,10 @@ struct Plan {
 // `ii`, `jj`: host copies of the edge lists. `M_expected`: rows of eta (ignored when < 0).
 bool build_plan(Plan& plan, const int64_t* ii, const int64_t* jj, int64_t E, int N, int t0, int t1,
                 bool motion_only, int64_t M_expected, int splits);
+// The same in two halves: what the linearisation needs (shape, CSR, slab offsets), then the gather lists that only the
+// assembly reads -- libdba builds the second half while the first linearisation of a new graph already runs.
+bool build_plan_csr(Plan& plan, const int64_t* ii, const int64_t* jj, int64_t E, int N, int t0, int t1,
+                    bool motion_only, int64_t M_expected, int splits);
+void build_plan_gather(Plan& plan);
 
 }  // namespace dba
