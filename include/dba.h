@@ -152,7 +152,9 @@ int dba_pgba(dba_ctx* ctx, float* poses, float* disps, const float* intrinsics, 
 /* ---- depth covariance of the Schur solve: the third output of BA (hislam2/geom/ba.py:98-107, chol.py:74-76;
  * SURVEY.md 8f rank 4).  Linearises at the GIVEN state exactly as one `ba` iteration would (same arguments, same
  * damping lm / ep), factors the reduced pose system and writes dzcov [M,ht,wd] = diag(E^T S^-1 E) Q^2 + Q, rows in
- * sorted(unique(ii)) order.  poses / disps are not modified. */
+ * sorted(unique(ii)) order.  poses / disps are not modified.  This call always linearises on the fp32 kernels (the
+ * "tensor_cores" option does not apply: S^-1 amplifies the coherent truncation of the tcgen05 accumulation) and keeps
+ * a plan of its own, so alternating with dba_ba on one graph rebuilds neither plan. */
 int dba_depth_cov(dba_ctx* ctx, const float* poses, const float* disps, const float* intrinsics, const float* disps_sens,
                   const float* targets, const float* weights, const float* eta, const int64_t* ii, const int64_t* jj,
                   int64_t E, int64_t N, int ht, int wd, int64_t M, int t0, int t1, float lm, float ep, float* dzcov_out,
