@@ -28,64 +28,7 @@ def _db():
     return droid_backends
 
 
-def _chain(P, r=1, skip_src=(), skip_dst=()):
-    e = [(i, j) for i in range(P) for j in range(P) if i != j and abs(i - j) <= r
-         and i not in skip_src and j not in skip_dst]
-    return [a for a, _ in e], [b for _, b in e]
-
-
-def _star(centre, leaves):
-    return [centre] * len(leaves), list(leaves)
-
-
-def _degree_mix():
-    """out-degree 20 / 21 (narrow | WIDE 1), 25 / 26 (WIDE 1 | WIDE 2), 41 / 42 (WIDE 2 | SIMT) next to a radius-2
-    chain (with radius 1 the chain ends hang on ONE edge: see _reference_fp32_gap)."""
-    P = 48
-    ii, jj = _chain(P, 2)
-    for centre, deg in ((3, 20), (4, 21), (5, 25), (6, 26), (7, 41), (8, 42)):
-        have = {j for i, j in zip(ii, jj) if i == centre}
-        leaves = [j for j in range(P - 1, -1, -1) if j != centre and j not in have][: deg - len(have)]
-        a, b = _star(centre, leaves)
-        ii += a
-        jj += b
-    return ii, jj
-
-
-def _random_graph(seed):
-    g = torch.Generator().manual_seed(seed)
-    P = int(torch.randint(3, 25, (1,), generator=g))
-    E = int(torch.randint(2, 6 * P, (1,), generator=g))
-    ii = torch.randint(0, P, (E,), generator=g)
-    jj = (ii + torch.randint(1, P, (E,), generator=g)) % P          # never a self edge; duplicates allowed
-    ht = int(torch.randint(3, 40, (1,), generator=g))
-    wd = int(torch.randint(3, 50, (1,), generator=g))
-    t0 = int(torch.randint(1, min(P - 1, 3) + 1, (1,), generator=g))
-    return dict(P=P, ht=ht, wd=wd, t0=t0, seed=seed, edges=(ii, jj))
-
-
-CASES = {
-    # frame 4 is never a source (no disparity row of its own: M = P - 1), frame 6 is never a target
-    "sink_and_source": dict(P=9, ht=20, wd=28, t0=1, seed=71, edges=_chain(9, 2, skip_src=(4,), skip_dst=(6,))),
-    # frame 5 sits inside the window with no edge at all: its pose block is damping only
-    "isolated_keyframe": dict(P=9, ht=20, wd=28, t0=2, seed=72, edges=_chain(9, 2, skip_src=(5,), skip_dst=(5,))),
-    # every edge twice, one of them three times (factor_graph.py never produces this; the scatter sums it)
-    "duplicate_edges": dict(P=6, ht=18, wd=26, t0=1, seed=73,
-                            edges=tuple(x * 2 + x[:1] for x in map(list, _chain(6, 2)))),
-    # t0 = 3: edges gauge -> gauge, gauge -> free, free -> gauge all present
-    "edges_inside_the_gauge": dict(P=8, ht=20, wd=28, t0=3, seed=74, edges=_chain(8, 3)),
-    "degree_thresholds": dict(P=48, ht=12, wd=20, t0=1, seed=75, edges=_degree_mix()),
-    "grid_below_one_tile": dict(P=6, ht=5, wd=7, t0=1, seed=76, edges=_chain(6, 2)),
-    "grid_exactly_one_tile": dict(P=6, ht=8, wd=16, t0=1, seed=77, edges=_chain(6, 2)),
-    "grid_one_over_a_tile": dict(P=6, ht=3, wd=43, t0=1, seed=78, edges=_chain(6, 2)),
-    "single_pair": dict(P=2, ht=16, wd=20, t0=1, seed=79, edges=([0, 1], [1, 0])),
-    "one_directed_edge": dict(P=3, ht=16, wd=20, t0=1, seed=80, edges=([1], [2])),
-    # ii == jj (projective_ops.py:53 has the stereo special case commented out: a self edge is a plain edge with Gij = 1);
-    # all four blocks of the edge land on the same diagonal block of H
-    "self_edges": dict(P=4, ht=16, wd=20, t0=1, seed=90, edges=([0, 1, 1, 2, 2, 3, 2, 3], [1, 0, 2, 1, 3, 2, 2, 3])),
-}
-for _s in range(100, 108):
-    CASES[f"random_{_s}"] = _random_graph(_s)
+from ragged_cases import CASES, chain as _chain, degree_mix as _degree_mix   # noqa: E402,F401
 
 
 def _oracle_step(p, dtype):
@@ -220,3 +163,33 @@ def test_pgba_on_ragged_graphs(name):
     src[p.ii] = True
     assert torch.equal(Dg.cpu()[~src], p.disps[~src])
     assert torch.equal(Pg.cpu()[: p.t0], poses8[: p.t0])
+
+
+import os  # noqa: E402
+
+import numpy as np  # noqa: E402
+
+from helpers import GOLDEN  # noqa: E402
+from ragged_cases import REFERENCE_PINNED  # noqa: E402
+
+RAGGED_REF = np.load(os.path.join(GOLDEN, "ragged.npz"))
+
+
+@pytest.mark.parametrize("name", REFERENCE_PINNED)
+def test_ragged_graph_matches_the_reference_itself(name):
+    """tests/golden/ragged.npz = the UNMODIFIED reference BA run on these graphs (oracle/make_golden_ragged.py): the
+    two-iteration CUDA call against its fp64 outputs, within a small multiple of the reference's OWN fp32-vs-fp64 gap."""
+    db = _db()
+    R = lambda k: torch.from_numpy(RAGGED_REF[f"{name}/{k}"])
+    p = make_problem(iters=2, **CASES[name])
+    g = p.to("cuda")
+    dxs = []
+    for _ in range(2):
+        dx, dz = db.ba(g.poses, g.disps, g.intrinsics, g.disps_sens, g.targets, g.weights, g.eta, g.ii, g.jj, g.t0, g.t1, 1,
+                       g.lm, g.ep, False)
+        dxs.append(dx.cpu())
+    gap0 = rel_err(R("ref_dx_f32")[0], R("ref_dx_f64")[0])
+    assert rel_err(dxs[0], R("ref_dx_f64")[0]) < MULT * gap0 + 1e-5, gap0
+    gap_d = rel_err(R("ref_disps_f32"), R("ref_disps_f64"))
+    assert rel_err(g.disps.cpu(), R("ref_disps_f64")) < max(1e-4, MULT * gap_d), gap_d
+    assert float((g.poses.cpu().double() - R("ref_poses_f64").double()).abs().max()) < 1e-4

@@ -52,3 +52,26 @@ def test_jacobians_match_reference(name):
     assert torch.equal(valid[sl], torch.from_numpy(g["jac_valid"]))
     for mine, key in ((coords, "jac_coords"), (Ji, "jac_Ji"), (Jj, "jac_Jj"), (Jz, "jac_Jz")):
         assert rel_err(mine[sl], g[key]) < 2e-6, key
+
+
+# ---- ragged / degenerate graphs: the reference itself run on them (oracle/make_golden_ragged.py) -------------------
+import os  # noqa: E402
+
+from cut3r_slam_b200.synthetic import make_problem  # noqa: E402
+from helpers import GOLDEN  # noqa: E402
+import ragged_cases  # noqa: E402
+
+RAGGED = np.load(os.path.join(GOLDEN, "ragged.npz"))
+
+
+@pytest.mark.parametrize("name", ragged_cases.REFERENCE_PINNED)
+def test_oracle_matches_reference_on_ragged_graphs(name):
+    """Keyframes without outgoing / incoming / any edges, duplicate and self edges, edges inside the gauge ...: the
+    restatement follows the reference's scatter and its unique(ii) row map on all of them (geom/ba.py:70-92)."""
+    p = make_problem(iters=2, **ragged_cases.CASES[name])
+    assert input_digest(p) == str(RAGGED[f"{name}/digest"])
+    poses, disps, infos = od.oracle_ba(*p.ba_args(), dtype=torch.float64, return_info=True)
+    for k, (dx, _) in enumerate(infos):
+        assert rel_err(dx, RAGGED[f"{name}/ref_dx_f64"][k]) < 1e-9, k
+    assert rel_err(disps, RAGGED[f"{name}/ref_disps_f64"]) < 1e-6
+    assert float((poses - torch.from_numpy(RAGGED[f"{name}/ref_poses_f64"])).abs().max()) < 1e-6

@@ -9,12 +9,13 @@ import oracle.se3 as ose3
 from helpers import rel_err
 from cut3r_slam_b200.synthetic import make_problem
 from cut3r_slam_b200 import droid_backends as db
-# the radius-1 variant of tests/test_ba_ragged_gpu.py's `degree_thresholds`: chain ends that hang on ONE edge
-_orig = t._chain
+# the radius-RADIUS variant of tests/ragged_cases.py's `degree_thresholds` (radius 1: chain ends that hang on ONE edge)
+import ragged_cases as rc
 RADIUS = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-t._chain = lambda P, r=1, **k: _orig(P, RADIUS, **k)
-kw = dict(t.CASES['degree_thresholds'], edges=t._degree_mix())
-t._chain = _orig
+_orig = rc.chain
+rc.chain = lambda P, r=1, **k: _orig(P, RADIUS, **k)
+kw = dict(rc.CASES['degree_thresholds'], edges=rc.degree_mix())
+rc.chain = _orig
 p = make_problem(iters=2, **kw)
 deg = torch.bincount(p.ii, minlength=48)
 for it in (1, 2):
