@@ -193,3 +193,19 @@ def test_ragged_graph_matches_the_reference_itself(name):
     gap_d = rel_err(R("ref_disps_f32"), R("ref_disps_f64"))
     assert rel_err(g.disps.cpu(), R("ref_disps_f64")) < max(1e-4, MULT * gap_d), gap_d
     assert float((g.poses.cpu().double() - R("ref_poses_f64").double()).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["sink_and_source", "isolated_keyframe", "self_edges", "random_101"])
+def test_depth_cov_matches_the_reference_itself_on_ragged_graphs(name):
+    """tests/golden/cov.npz `ragged_*` = the third output of the UNMODIFIED reference BA on these graphs
+    (oracle/make_golden_cov.py); bound: 1e-4 per pixel or 3x the reference's own fp32-vs-fp64 gap."""
+    db = _db()
+    cov_gold = np.load(os.path.join(GOLDEN, "cov.npz"))
+    ref = torch.from_numpy(cov_gold[f"ragged_{name}_dzcov_f64"])
+    ref32 = torch.from_numpy(cov_gold[f"ragged_{name}_dzcov_f32"]).double()
+    p = make_problem(iters=1, **CASES[name])
+    g = p.to("cuda")
+    cov = db.depth_cov(g.poses, g.disps, g.intrinsics, None, g.targets, g.weights, g.eta, g.ii, g.jj, p.t0, p.t1, p.lm, p.ep)
+    got = cov.cpu().double().reshape(ref.shape)
+    gap = float(((ref32 - ref).abs() / ref.abs()).max())
+    assert float(((got - ref).abs() / ref.abs()).max()) < max(1e-4, MULT * gap), gap

@@ -25,3 +25,20 @@ def test_depth_cov_matches_reference(name):
     assert cov.shape == ref.shape
     assert float(((cov - ref).abs() / ref.abs()).max()) < 1e-10
     assert float(cov.min()) > 0                                       # Q plus a positive semi-definite term
+
+
+RAGGED = ["sink_and_source", "isolated_keyframe", "self_edges", "random_101"]     # oracle/make_golden_cov.py RAGGED
+
+
+@pytest.mark.parametrize("name", RAGGED)
+def test_depth_cov_matches_reference_on_ragged_graphs(name):
+    """Rows follow sorted(unique(ii)) (frame 4 of `sink_and_source` has no row), an isolated keyframe contributes only
+    its damping, a self edge adds all four of its blocks to one diagonal block."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ragged_cases
+    from cut3r_slam_b200.synthetic import make_problem
+    p = make_problem(iters=1, **ragged_cases.CASES[name])
+    cov = od.depth_cov(p.poses, p.disps, p.intrinsics, None, p.targets, p.weights, p.eta, p.ii, p.jj, p.t0, p.t1, p.lm, p.ep)
+    ref = torch.from_numpy(GOLD[f"ragged_{name}_dzcov_f64"])
+    assert cov.shape == ref.shape
+    assert float(((cov - ref).abs() / ref.abs()).max()) < 1e-9
