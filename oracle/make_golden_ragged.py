@@ -36,6 +36,26 @@ def main():
             rec[f"{name}/ref_disps_{tag}"] = nd.numpy()
             rec[f"{name}/ref_dx_{tag}"] = torch.stack(dxs).to(torch.float64).numpy()
         print(name, "E", int(p.ii.numel()), "dx max per iteration", [float(np.abs(d).max()) for d in rec[f"{name}/ref_dx_f32"]])
+    # the same graphs through the reference's MoBA (geom/ba.py:110-158) ...
+    for name in ragged_cases.REFERENCE_PINNED_MOBA:
+        p = make_problem(iters=2, **ragged_cases.CASES[name])
+        for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+            np_, nd, dxs = ref_harness.ref_ba(p.poses, p.disps, p.intrinsics, p.targets, p.weights, p.eta, p.ii, p.jj, p.t0,
+                                              p.t1, p.iterations, p.lm, p.ep, True, dtype=dt)
+            rec[f"{name}/moba_poses_{tag}"] = np_.numpy()
+            rec[f"{name}/moba_dx_{tag}"] = torch.stack(dxs).to(torch.float64).numpy()
+        print(name, "MoBA dx max per iteration", [float(np.abs(d).max()) for d in rec[f"{name}/moba_dx_f32"]])
+    # ... and through its BA with lietorch.Sim3 poses (the 7-dof linearisation of pgba), scales as in the tests
+    from .make_golden_pgba import ref_ba_sim3
+    for name in ragged_cases.REFERENCE_PINNED_SIM3:
+        p = make_problem(iters=2, **ragged_cases.CASES[name])
+        poses8 = torch.cat([p.poses, ragged_cases.sim3_scales(p.poses.shape[0], p.t0)], -1)
+        for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+            P8, d, dxs = ref_ba_sim3(p, poses8, dt)
+            rec[f"{name}/sim3_poses_{tag}"] = P8.numpy()
+            rec[f"{name}/sim3_disps_{tag}"] = d.numpy()
+            rec[f"{name}/sim3_dx_{tag}"] = dxs.to(torch.float64).numpy()
+        print(name, "Sim3 dx max per iteration", [float(np.abs(d).max()) for d in rec[f"{name}/sim3_dx_f32"]])
     path = os.path.join(ROOT, "tests", "golden", "ragged.npz")
     np.savez_compressed(path, **rec)
     print(path, os.path.getsize(path), "bytes")

@@ -65,3 +65,14 @@ for _s in range(100, 108):
 # the cases oracle/make_golden_ragged.py runs through the reference itself (tests/golden/ragged.npz)
 REFERENCE_PINNED = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "edges_inside_the_gauge", "self_edges",
                     "one_directed_edge", "grid_below_one_tile", "random_101", "random_107"]
+REFERENCE_PINNED_MOBA = ["sink_and_source", "isolated_keyframe", "self_edges", "random_101"]
+REFERENCE_PINNED_SIM3 = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "self_edges", "random_107"]
+# the CUDA pgba is held to the reference on these; `isolated_keyframe` is pinned for the oracle only (see the GPU test)
+GPU_SIM3 = ["sink_and_source", "duplicate_edges", "self_edges", "random_107"]
+
+
+def sim3_scales(P, t0):
+    """Per-frame scales of the Sim3 cases: 1 +- 5 %, gauge frames at 1."""
+    s = 1.0 + 0.05 * (2 * torch.rand(P, 1, generator=torch.Generator().manual_seed(3)) - 1)
+    s[:t0] = 1.0
+    return s

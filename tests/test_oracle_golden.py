@@ -75,3 +75,29 @@ def test_oracle_matches_reference_on_ragged_graphs(name):
         assert rel_err(dx, RAGGED[f"{name}/ref_dx_f64"][k]) < 1e-9, k
     assert rel_err(disps, RAGGED[f"{name}/ref_disps_f64"]) < 1e-6
     assert float((poses - torch.from_numpy(RAGGED[f"{name}/ref_poses_f64"])).abs().max()) < 1e-6
+
+
+@pytest.mark.parametrize("name", ragged_cases.REFERENCE_PINNED_MOBA)
+def test_oracle_moba_matches_reference_on_ragged_graphs(name):
+    """The reference's MoBA (geom/ba.py:110-158, block_solve as written) on the same graphs."""
+    p = make_problem(iters=2, **ragged_cases.CASES[name])
+    p.motion_only = True
+    poses, disps, infos = od.oracle_ba(*p.ba_args(), dtype=torch.float64, block_diag_quirk=True, return_info=True)
+    for k, (dx, _) in enumerate(infos):
+        assert rel_err(dx, RAGGED[f"{name}/moba_dx_f64"][k]) < 1e-9, k
+    assert float((poses - torch.from_numpy(RAGGED[f"{name}/moba_poses_f64"])).abs().max()) < 1e-6
+    assert torch.equal(disps, p.disps)
+
+
+@pytest.mark.parametrize("name", ragged_cases.REFERENCE_PINNED_SIM3)
+def test_oracle_sim3_ba_matches_reference_on_ragged_graphs(name):
+    """The reference's BA with lietorch.Sim3 poses (the 7-dof linearisation of pgba) on the same graphs."""
+    import oracle.pgba as op
+    p = make_problem(iters=2, **ragged_cases.CASES[name])
+    poses8 = torch.cat([p.poses, ragged_cases.sim3_scales(p.poses.shape[0], p.t0)], -1)
+    poses, disps, infos = op.oracle_pgba(poses8, p.disps, p.intrinsics, p.targets, p.weights, p.eta, p.ii, p.jj, None, None,
+                                         None, None, p.t0, p.t1, 2, p.lm, p.ep, 0.0, dtype=torch.float64, return_info=True)
+    for k in range(2):
+        assert rel_err(infos[k][0], RAGGED[f"{name}/sim3_dx_f64"][k]) < 1e-9, k
+    assert rel_err(disps.double(), RAGGED[f"{name}/sim3_disps_f64"]) < 1e-6
+    assert rel_err(poses.double(), RAGGED[f"{name}/sim3_poses_f64"]) < 1e-6
