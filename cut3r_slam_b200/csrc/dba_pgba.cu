@@ -618,13 +618,19 @@ __global__ void __launch_bounds__(128)
 k_pg_retract(float* __restrict__ poses, const float* __restrict__ dx, int t0, int Pp, float* __restrict__ dx_out) {
   const int a = blockIdx.x * 128 + threadIdx.x;
   if (a >= Pp) return;
-  float xi[7];
-  for (int k = 0; k < 7; ++k) { xi[k] = dx[a * 7 + k]; if (dx_out) dx_out[a * 7 + k] = xi[k]; }
+  // Exp in fp64: the scale updates of a converging solve are 1e-6 .. 1e-5, where W's coefficient C = (e^sigma - 1) / sigma
+  // (rxso3.h:190-233, general branch above |sigma| = 1e-6) keeps two digits in fp32 and B none -- the translation of
+  // Exp(dx) is then off by ~1 % of |tau| (3e-4 on a 2e-2 step; tools/sim3_state_diag.py: the state after one iteration
+  // was 2.8e-4 from the fp64 result, and the NEXT update 1.7e-2 off, although this update was exact to 6e-5).  The
+  // reference evaluates the same formulas in fp32 and carries the same noise (its own fp32 run: 3.6e-3 on that update);
+  // one thread per pose makes fp64 free here.
+  double xi[7];
+  for (int k = 0; k < 7; ++k) { xi[k] = double(dx[a * 7 + k]); if (dx_out) dx_out[a * 7 + k] = dx[a * 7 + k]; }
   float* p = poses + 8 * (t0 + a);
-  const S3<float> g = s3_mul(s3_exp(xi), s3_load<float>(p));
-  p[0] = g.t[0]; p[1] = g.t[1]; p[2] = g.t[2];
-  p[3] = g.q[0]; p[4] = g.q[1]; p[5] = g.q[2]; p[6] = g.q[3];
-  p[7] = g.s;
+  const S3<double> g = s3_mul(s3_exp(xi), s3_load<double>(p));
+  p[0] = float(g.t[0]); p[1] = float(g.t[1]); p[2] = float(g.t[2]);
+  p[3] = float(g.q[0]); p[4] = float(g.q[1]); p[5] = float(g.q[2]); p[6] = float(g.q[3]);
+  p[7] = float(g.s);
 }
 
 }  // namespace

@@ -67,8 +67,8 @@ REFERENCE_PINNED = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "
                     "one_directed_edge", "grid_below_one_tile", "random_101", "random_107"]
 REFERENCE_PINNED_MOBA = ["sink_and_source", "isolated_keyframe", "self_edges", "random_101"]
 REFERENCE_PINNED_SIM3 = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "self_edges", "random_107"]
-# the CUDA pgba is held to the reference on these; `isolated_keyframe` is pinned for the oracle only (see the GPU test)
-GPU_SIM3 = ["sink_and_source", "duplicate_edges", "self_edges", "random_107"]
+# the CUDA pgba is held to the reference on these
+GPU_SIM3 = ["sink_and_source", "isolated_keyframe", "duplicate_edges", "self_edges", "random_107"]
 
 
 def sim3_scales(P, t0):

@@ -237,11 +237,10 @@ def test_ragged_moba_matches_the_reference_itself(name):
 @pytest.mark.parametrize("name", GPU_SIM3)
 def test_ragged_sim3_ba_matches_the_reference_itself(name):
     """pgba without relative-pose factors on the same graphs against the reference's BA run with lietorch.Sim3 poses.
-    Measured (tools/sim3_ragged_diag.py, bit-identical run to run): the first iteration sits at 0.04 - 0.12x the
-    reference's own fp32 gap, the SECOND at 2.6x on `sink_and_source` and 4.7x on `isolated_keyframe` (1.7e-2 of a 1.4e-2
-    update, the reference's fp32 run 3.6e-3; worst row: the chain-end keyframe) -- the state the SIMT Sim3 path leaves
-    after one iteration is noisier than the reference's fp32 state at weakly observed frames.  `isolated_keyframe` is
-    therefore pinned for the restatement only (tests/test_oracle_golden.py); open item in DESIGN.md section 9, row 1."""
+    These cases found the fp32 Sim3 retraction: scale updates of 1e-6 .. 1e-5 leave (e^sigma - 1) / sigma two digits in
+    fp32, the state after one iteration was 2.8e-4 off and the SECOND update 4.7x the reference's own fp32 gap on
+    `isolated_keyframe` (tools/sim3_state_diag.py).  With Exp(dx) in fp64 (k_pg_retract) both iterations sit at
+    0.02 - 0.12x that gap (tools/sim3_ragged_diag.py)."""
     db = _db()
     R = lambda k: torch.from_numpy(RAGGED_REF[f"{name}/{k}"])
     p = make_problem(iters=2, **CASES[name])
