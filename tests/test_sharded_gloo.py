@@ -105,3 +105,25 @@ def test_partition_properties():
             assert bool((s["edges"][1:] > s["edges"][:-1]).all())                    # original edge order kept
         cost = [float(((torch.bincount(p.ii[s["edges"]]).double() + 1) ** 2).sum()) for s in shards if s["edges"].numel()]
         assert max(cost) < 2.5 * (sum(cost) / len(cost))                             # balanced on Schur cost
+
+
+def test_partition_of_ragged_graphs():
+    """More ranks than source keyframes, a single edge, source keyframes with gaps: every edge lands on exactly one rank,
+    shards stay contiguous in sorted(unique(ii)), ranks without work get an empty (not a missing) shard -- such a rank
+    still calls `ba` with E = 0 and takes part in the all-reduce of the reduced system."""
+    import ragged_cases
+    for name in ("one_directed_edge", "single_pair", "sink_and_source", "isolated_keyframe", "self_edges", "random_105"):
+        ii = torch.as_tensor(ragged_cases.CASES[name]["edges"][0], dtype=torch.long)
+        kx = torch.unique(ii)
+        for world in (1, 2, 3, 8):
+            shards = partition_by_source(ii, world)
+            assert len(shards) == world
+            edges = torch.cat([s["edges"] for s in shards])
+            assert torch.equal(torch.sort(edges).values, torch.arange(ii.numel()))
+            assert torch.equal(torch.cat([s["keyframes"] for s in shards]), kx)
+            lo = 0
+            for s in shards:
+                assert s["slots"][0] == lo and s["slots"][1] == lo + s["keyframes"].numel()
+                lo = s["slots"][1]
+                assert torch.equal(torch.unique(ii[s["edges"]]), s["keyframes"])
+            assert lo == kx.numel()
