@@ -72,6 +72,24 @@ def test_gather_lists_reproduce_reference_scatter(kw):
         p.jj[3] = p.jj[2] if p.ii[3] == p.ii[2] else p.jj[3]
         p.jj[5] = p.ii[5]
         p.jj[9] = p.jj[8] if p.ii[9] == p.ii[8] else p.jj[9]
+    _check_gather_lists(p)
+
+
+def _ragged_names():
+    import ragged_cases
+    return list(ragged_cases.CASES)
+
+
+@pytest.mark.parametrize("name", _ragged_names())
+def test_gather_lists_on_ragged_graphs(name):
+    """The plan of every ragged / degenerate graph of tests/ragged_cases.py (keyframes without outgoing / incoming / any
+    edges, duplicate and self edges, hubs of out-degree 42, random graphs) replays to the reference's scatter."""
+    import ragged_cases
+    kw = dict(ragged_cases.CASES[name], ht=5, wd=6)         # the plan does not depend on the grid
+    _check_gather_lists(make_problem(iters=1, **kw))
+
+
+def _check_gather_lists(p):
     f = lambda t: t.double()
     tgt, wgt = f(p.targets).permute(0, 2, 3, 1), f(p.weights).permute(0, 2, 3, 1)
     lin = od.linearize(tgt, wgt, f(p.eta), f(p.poses), f(p.disps), f(p.intrinsics), p.ii, p.jj, p.t0)
