@@ -92,3 +92,20 @@ def test_butterfly_index_map():
                 new[lane, i] = keep + recv
         v, cnt, mask = new, half, mask // 2
     assert torch.equal(v[:, 0], vals.sum(0))
+
+
+def test_sim3_translation_coefficient_needs_fp64_for_small_scale_updates():
+    """Why k_pg_retract evaluates Exp(dx) in fp64: W = A Phi + B Phi^2 + C I with C = (e^sigma - 1) / sigma
+    (rxso3.h:190-233) multiplies tau directly.  The formula's series branch starts below |sigma| = 1e-6; the scale updates
+    of a converging solve are 1e-6 .. 1e-5, where fp32 keeps about two digits of C."""
+    import numpy as np
+    worst32, worst64 = 0.0, 0.0
+    for sigma in (2.5e-6, 4.7e-6, 6.5e-6, 1.2e-5, -7.5e-6, -1.3e-5):
+        exact = float(np.expm1(np.float64(sigma)) / np.float64(sigma))
+        s32 = np.float32(sigma)
+        c32 = float((np.exp(s32, dtype=np.float32) - np.float32(1)) / s32)
+        c64 = float((np.exp(np.float64(sigma)) - 1.0) / np.float64(sigma))
+        worst32 = max(worst32, abs(c32 - exact) / exact)
+        worst64 = max(worst64, abs(c64 - exact) / exact)
+    assert worst32 > 1e-3            # fp32: 0.1 % .. several % of tau
+    assert worst64 < 1e-9            # fp64: far below the fp32 rounding of the stored pose
